@@ -1,0 +1,68 @@
+"""ctypes binding of libf2f_b200.so (include/f2f_b200.h).
+
+The product path has no CPU fallback: if the library is missing or a call
+fails, a RuntimeError is raised.
+"""
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "lib", "libf2f_b200.so")
+
+_lib = None
+
+
+class Tvl1Params(C.Structure):
+    """struct f2f_tvl1_params (include/f2f_b200.h); defaults of main.c:25-35."""
+    _fields_ = [("tau", C.c_float), ("lam", C.c_float), ("theta", C.c_float),
+                ("nscales", C.c_int), ("fscale", C.c_int), ("zfactor", C.c_float),
+                ("nwarps", C.c_int), ("epsilon", C.c_float), ("verbose", C.c_int)]
+
+
+def _declare(lib):
+    vp, fp, ip, sz = C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t
+    lib.f2f_last_error.restype = C.c_char_p
+    lib.f2f_tvl1_default_params.argtypes = [C.POINTER(Tvl1Params)]
+    lib.f2f_tvl1_default_params.restype = None
+    lib.f2f_tvl1_validate_params.argtypes = [C.POINTER(Tvl1Params), C.c_int, C.c_int]
+    lib.f2f_tvl1_zoom_size.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_float]
+    lib.f2f_tvl1_zoom_size.restype = None
+    lib.f2f_tvl1_workspace_bytes.argtypes = [C.c_int, C.c_int, C.POINTER(Tvl1Params), C.c_int]
+    lib.f2f_tvl1_workspace_bytes.restype = sz
+    lib.f2f_tvl1_flow_batch.argtypes = [fp, fp, fp, C.c_int, C.c_int, C.c_int, C.POINTER(Tvl1Params), ip, vp, sz, vp]
+    lib.f2f_tvl1_flow_batch_host.argtypes = [fp, fp, fp, C.c_int, C.c_int, C.c_int, C.POINTER(Tvl1Params), ip, C.c_int]
+    lib.f2f_tvl1_gaussian.argtypes = [fp, C.c_int, C.c_int, C.c_double, fp, vp]
+    lib.f2f_tvl1_zoom_out.argtypes = [fp, fp, C.c_int, C.c_int, C.c_float, fp, vp]
+    lib.f2f_tvl1_zoom_in_scaled.argtypes = [fp, fp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, vp]
+    lib.f2f_tvl1_centered_gradient.argtypes = [fp, fp, fp, C.c_int, C.c_int, vp]
+    lib.f2f_tvl1_normalize.argtypes = [fp, fp, fp, fp, C.c_int, C.c_int, vp, vp]
+    lib.f2f_release.restype = None
+
+
+def lib():
+    """The loaded library; raises if it has not been built (no fallback)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                "libf2f_b200.so is not built (%s); run `python -m frame2frame_b200.build`. "
+                "There is no CPU fallback." % LIB_PATH)
+        _lib = C.CDLL(LIB_PATH)
+        _declare(_lib)
+    return _lib
+
+
+def check(rc, what):
+    if rc != 0:
+        msg = lib().f2f_last_error()
+        raise RuntimeError("%s failed (code %d): %s" % (what, rc, msg.decode() if msg else ""))
+
+
+def exported_symbols():
+    """Names declared in include/f2f_b200.h (parsed), for the ABI test."""
+    import re
+    hdr = os.path.join(os.path.dirname(HERE), "include", "f2f_b200.h")
+    text = open(hdr).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    names = re.findall(r"\b(f2f_\w+|Dual_TVL1_optic_flow_multiscale)\s*\(", text)
+    return sorted(set(n for n in names if not n.startswith("f2f_tvl1_params")))

@@ -1,0 +1,127 @@
+/*
+ * f2f_b200.h -- C ABI of libf2f_b200.so, the B200 (sm_100a) implementation of
+ * the frame2frame hot path.  Plain pointers and sizes only; no torch types.
+ *
+ * Conventions
+ *  - "d_" pointers are device pointers owned by the caller (e.g. torch
+ *    tensors' data_ptr()); "h_" pointers are host pointers.
+ *  - `stream` is a cudaStream_t passed as void* (0 = default stream).
+ *  - every function returns F2F_OK (0) or a negative F2F_E* code; the text of
+ *    the last error of the calling thread is available from f2f_last_error().
+ *    Where the reference exits/aborts (xmalloc.c:16-22, mask.c:238-241,
+ *    main.c:189-193) this library returns an error code instead.
+ *  - images are row-major float32, `nx` = width, `ny` = height, exactly as in
+ *    the reference's C code; flows are planar (u1 plane then u2 plane), the
+ *    layout main.c:173-174 allocates and `read_flow(...).permute(2,0,1)`
+ *    (blind_denoising.py:206-209) produces.
+ *
+ * Citations are into the reference tree (gauenk/frame2frame).
+ */
+#ifndef F2F_B200_H
+#define F2F_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+#include <stdbool.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define F2F_OK 0
+#define F2F_EINVAL (-1)   /* bad argument                                   */
+#define F2F_ESIGMA (-2)   /* "GaussianSmooth: sigma too large" mask.c:238   */
+#define F2F_ENOMEM (-3)   /* workspace too small / allocation failed        */
+#define F2F_ECUDA (-4)    /* CUDA runtime error (see f2f_last_error)        */
+
+const char *f2f_last_error(void);
+/* Library/ABI version and the SM architecture the kernels were built for. */
+int f2f_version(void);
+int f2f_built_sm(void);
+
+/* ------------------------------------------------------------------ TV-L1 */
+
+/* Parameters of tvl1flow (main.c:86-99 positional arguments 5..13). */
+typedef struct f2f_tvl1_params {
+    float tau;      /* time step                  default 0.25 (main.c:27) */
+    float lambda;   /* data term weight           default 0.15 (main.c:28) */
+    float theta;    /* tightness                  default 0.3  (main.c:29) */
+    int nscales;    /* pyramid levels             default 100  (main.c:30) */
+    int fscale;     /* finest scale computed      default 0    (main.c:31) */
+    float zfactor;  /* pyramid zoom factor        default 0.5  (main.c:32) */
+    int nwarps;     /* warps per scale            default 5    (main.c:33) */
+    float epsilon;  /* stopping threshold         default 0.01 (main.c:34) */
+    int verbose;    /* print per-warp iteration counts to stderr (main.c:35) */
+} f2f_tvl1_params;
+
+/* main.c:25-35 */
+void f2f_tvl1_default_params(f2f_tvl1_params *p);
+/* main.c:102-141 (out-of-range values reset to defaults) followed by the
+ * image-size dependent clamp of nscales/fscale, main.c:159-163.  Must be
+ * applied before f2f_tvl1_flow_batch, like main() does before calling
+ * Dual_TVL1_optic_flow_multiscale. */
+int f2f_tvl1_validate_params(f2f_tvl1_params *p, int nx, int ny);
+/* zoom.c:24-36 */
+void f2f_tvl1_zoom_size(int nx, int ny, int *nxx, int *nyy, float factor);
+
+/* Bytes of device workspace needed to process `nslots` frame pairs
+ * concurrently (params already validated).  Returns 0 on bad arguments. */
+size_t f2f_tvl1_workspace_bytes(int nx, int ny, const f2f_tvl1_params *p, int nslots);
+
+/* Replaces Dual_TVL1_optic_flow_multiscale (tvl1flow_lib.c:356-372) for a
+ * batch of independent frame pairs resident in HBM.
+ *   d_I0, d_I1 : [npairs][ny][nx] float32 (any value range; normalised inside
+ *                as tvl1flow_lib.c:314-348 does)
+ *   d_u        : [npairs][2][ny][nx] float32 out (u1 plane, u2 plane)
+ *   h_iters    : optional host int32 [npairs][nscales][nwarps]: inner
+ *                iterations run per (scale, warp) -- what `verbose` prints at
+ *                tvl1flow_lib.c:259-262; rows of scales < fscale are 0.
+ *   d_workspace: >= f2f_tvl1_workspace_bytes(nx, ny, p, nslots) for some
+ *                nslots >= 1; pairs are processed nslots at a time.
+ * Synchronises `stream` before returning iff h_iters != NULL or verbose. */
+int f2f_tvl1_flow_batch(const float *d_I0, const float *d_I1, float *d_u,
+                        int npairs, int nx, int ny, const f2f_tvl1_params *p,
+                        int32_t *h_iters, void *d_workspace, size_t ws_bytes,
+                        void *stream);
+
+/* Same, for HOST buffers: uploads the frames, runs the batch and downloads the
+ * flows (device memory is allocated inside and cached between calls; release
+ * with f2f_release()).  This is the call a host program that used to run one
+ * `tvl1flow` process per pair (tvl1flow.sh:9-19) makes instead.
+ * max_slots <= 0 picks a default. */
+int f2f_tvl1_flow_batch_host(const float *h_I0, const float *h_I1, float *h_u,
+                             int npairs, int nx, int ny, const f2f_tvl1_params *p,
+                             int32_t *h_iters, int max_slots);
+
+/* Drop-in for the reference symbol, same signature and host-pointer semantics
+ * (tvl1flow_lib.c:356-372): a main.c linked against this library instead of
+ * #including tvl1flow_lib.c runs unchanged.  Aborts on error like the
+ * reference does. */
+void Dual_TVL1_optic_flow_multiscale(float *I0, float *I1, float *u1, float *u2,
+                                     const int nxx, const int nyy, const float tau,
+                                     const float lambda, const float theta,
+                                     const int nscales, const int fscale,
+                                     const float zfactor, const int warps,
+                                     const float epsilon, const bool verbose);
+
+/* Stage-level entry points (device pointers), exported so that each kernel can
+ * be parity-tested against the reference function it replaces. */
+int f2f_tvl1_gaussian(float *d_I, int nx, int ny, double sigma, float *d_tmp,
+                      void *stream);                       /* mask.c:223-339  */
+int f2f_tvl1_zoom_out(const float *d_I, float *d_out, int nx, int ny, float factor,
+                      float *d_tmp2, void *stream);        /* zoom.c:43-81 (d_tmp2: 2*nx*ny) */
+int f2f_tvl1_zoom_in_scaled(const float *d_I, float *d_out, int nx, int ny, int nxx,
+                            int nyy, float zfactor, void *stream); /* zoom.c:89-115 + tvl1flow_lib.c:442-446 */
+int f2f_tvl1_centered_gradient(const float *d_I, float *d_dx, float *d_dy, int nx,
+                               int ny, void *stream);      /* mask.c:156-215  */
+int f2f_tvl1_normalize(const float *d_I0, const float *d_I1, float *d_I0n,
+                       float *d_I1n, int nx, int ny, void *d_scratch8,
+                       void *stream);                      /* tvl1flow_lib.c:314-348 */
+
+/* Release every cached device allocation of the calling process. */
+void f2f_release(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* F2F_B200_H */

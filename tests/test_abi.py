@@ -1,0 +1,58 @@
+"""CPU tests of the drop-in boundary: the C-ABI library loads and exports every
+symbol include/f2f_b200.h declares; host-side parameter logic (no compute)."""
+import ctypes as C
+
+import numpy as np
+
+from frame2frame_b200 import _lib
+from frame2frame_b200.tvl1 import make_params, read_flo, write_flo
+from oracle.tvl1 import clamp_scales
+
+
+def test_library_exports_every_declared_symbol():
+    lib = _lib.lib()
+    names = _lib.exported_symbols()
+    assert "f2f_tvl1_flow_batch" in names and "Dual_TVL1_optic_flow_multiscale" in names
+    for n in names:
+        assert hasattr(lib, n), "missing export: " + n
+    assert lib.f2f_built_sm() == 100
+
+
+def test_default_params_are_main_c_defaults():
+    p = _lib.Tvl1Params()
+    _lib.lib().f2f_tvl1_default_params(C.byref(p))
+    assert (round(p.tau, 6), round(p.lam, 6), round(p.theta, 6), p.nscales, p.fscale, round(p.zfactor, 6), p.nwarps,
+            round(p.epsilon, 6), p.verbose) == (0.25, 0.15, 0.3, 100, 0, 0.5, 5, 0.01, 0)
+
+
+def test_validate_resets_and_clamps_like_main_c():
+    p = make_params(1920, 1080, tau=0.5, lam=-1, theta=0, nscales=0, zfactor=1.5, nwarps=0, epsilon=-3)
+    assert (round(p.tau, 6), round(p.lam, 6), round(p.theta, 6), round(p.zfactor, 6), p.nwarps) == (0.25, 0.15, 0.3, 0.5, 5)
+    for (nx, ny, z, ns, fs) in [(1920, 1080, 0.5, 100, 0), (3840, 2160, 0.5, 100, 2), (960, 540, 0.5, 5, 0),
+                                (120, 68, 0.5, 100, 9), (640, 480, 0.75, 100, 0)]:
+        p = make_params(nx, ny, zfactor=z, nscales=ns, fscale=fs)
+        assert (p.nscales, p.fscale) == clamp_scales(nx, ny, z, ns, fs)
+
+
+def test_workspace_bytes_and_bad_args():
+    lib = _lib.lib()
+    p = make_params(1920, 1080, nscales=5)
+    b1 = lib.f2f_tvl1_workspace_bytes(1920, 1080, C.byref(p), 1)
+    b4 = lib.f2f_tvl1_workspace_bytes(1920, 1080, C.byref(p), 4)
+    assert 0 < b1 < b4 < 4 * b1 + 4096
+    assert lib.f2f_tvl1_workspace_bytes(2, 2, C.byref(p), 1) == 0
+    assert lib.f2f_tvl1_workspace_bytes(1920, 1080, C.byref(p), 0) == 0
+
+
+def test_flo_roundtrip_matches_reference_layout(tmp_path):
+    # readFlowFile.py:18-34: float32 tag 202021.25, int32 w, int32 h, h*w*2 float32 interleaved
+    flow = np.arange(2 * 3 * 5, dtype=np.float32).reshape(2, 3, 5)
+    path = str(tmp_path / "x.flo")
+    write_flo(path, flow)
+    raw = open(path, "rb").read()
+    assert len(raw) == 12 + 2 * 3 * 5 * 4
+    assert np.frombuffer(raw[:4], np.float32)[0] == np.float32(202021.25)
+    assert tuple(np.frombuffer(raw[4:12], np.int32)) == (5, 3)
+    back = read_flo(path)
+    assert back.shape == (3, 5, 2)
+    assert np.array_equal(back.transpose(2, 0, 1), flow)

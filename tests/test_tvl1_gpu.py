@@ -1,0 +1,129 @@
+"""GPU parity tests: CUDA TV-L1 (through the C ABI) against the oracle.
+
+Bar (BASELINE.json north_star): flow within 1e-3 px max-abs of the OpenMP
+reference and -- because one extra/missing inner iteration already moves the
+flow by ~0.01 px -- identical per-(scale, warp) iteration counts.
+"""
+import ast
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from frame2frame_b200 import _lib, synth
+from frame2frame_b200.tvl1 import tvl1flow, tvl1flow_host
+from oracle.tvl1 import OracleTvl1
+
+pytestmark = pytest.mark.gpu
+GOLD = np.load(os.path.join(os.path.dirname(__file__), "golden", "tvl1_ref.npz"))
+FLOW_TOL = 1e-3  # px, north_star
+
+
+def dev(a, cuda):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(cuda)
+
+
+def _stage(cuda, fn, *arrs):
+    return [dev(a, cuda) for a in arrs]
+
+
+def test_stage_kernels_bit_exact(cuda):
+    lib = _lib.lib()
+    o = OracleTvl1()
+    for (H, W) in [(33, 47), (135, 240)]:
+        I0, I1 = synth.noisy_frame(H, W, 3), synth.noisy_frame(H, W, 2)
+        # gaussian, mask.c:223-339
+        d = dev(I0, cuda)
+        tmp = torch.empty_like(d)
+        _lib.check(lib.f2f_tvl1_gaussian(d.data_ptr(), W, H, 0.8, tmp.data_ptr(), None), "gaussian")
+        assert np.array_equal(d.cpu().numpy(), o.gaussian(I0, 0.8))
+        # zoom_out, zoom.c:43-81
+        for f in (0.5, 0.7):
+            ref = o.zoom_out(I0, f)
+            out = torch.empty(ref.shape, device=cuda)
+            tmp2 = torch.empty(2 * H * W, device=cuda)
+            src = dev(I0, cuda)   # keep a reference: a temporary would be freed before the kernel runs
+            _lib.check(lib.f2f_tvl1_zoom_out(src.data_ptr(), out.data_ptr(), W, H, f, tmp2.data_ptr(), None), "zoom_out")
+            assert np.array_equal(out.cpu().numpy(), ref)
+        # zoom_in + rescale
+        z = o.zoom_out(I0, 0.5)
+        out = torch.empty((H, W), device=cuda)
+        dz = dev(z, cuda)
+        _lib.check(lib.f2f_tvl1_zoom_in_scaled(dz.data_ptr(), out.data_ptr(), z.shape[1], z.shape[0], W, H, 0.5, None), "zoom_in")
+        assert np.array_equal(out.cpu().numpy(), o.zoom_in_scaled(z, W, H, 0.5))
+        # centered gradient
+        dx, dy = torch.empty((H, W), device=cuda), torch.empty((H, W), device=cuda)
+        src = dev(I0, cuda)
+        _lib.check(lib.f2f_tvl1_centered_gradient(src.data_ptr(), dx.data_ptr(), dy.data_ptr(), W, H, None), "cgrad")
+        rx, ry = o.centered_gradient(I0)
+        assert np.array_equal(dx.cpu().numpy(), rx) and np.array_equal(dy.cpu().numpy(), ry)
+        # normalisation (arbitrary value range, negative minimum)
+        a, b = I0 * 0.3 - 7, I1 * 0.3 - 7
+        oa, ob = torch.empty((H, W), device=cuda), torch.empty((H, W), device=cuda)
+        scratch = torch.empty(8, dtype=torch.uint8, device=cuda)
+        da, db = dev(a, cuda), dev(b, cuda)
+        _lib.check(lib.f2f_tvl1_normalize(da.data_ptr(), db.data_ptr(), oa.data_ptr(), ob.data_ptr(), W, H, scratch.data_ptr(), None), "normalize")
+        ra, rb = o.normalize(a, b)
+        assert np.array_equal(oa.cpu().numpy(), ra) and np.array_equal(ob.cpu().numpy(), rb)
+
+
+@pytest.mark.parametrize("case", ["a", "b", "c"])
+def test_flow_matches_reference_golden(cuda, case):
+    H, W = GOLD[case + "_hw"]
+    kw = ast.literal_eval(str(GOLD[case + "_kw"]))
+    I0, I1 = synth.noisy_frame(H, W, 1), synth.noisy_frame(H, W, 0)
+    flow, iters = tvl1flow(dev(I0, cuda), dev(I1, cuda), return_iters=True, **kw)
+    assert np.array_equal(iters, GOLD[case + "_iters"]), (iters, GOLD[case + "_iters"])
+    diff = np.abs(flow.cpu().numpy() - GOLD[case + "_flow"]).max()
+    assert diff <= FLOW_TOL, diff
+
+
+def test_batch_of_pairs_vs_oracle_and_host_api(cuda):
+    # ragged batch (7 pairs, 3 slots): every pair must equal its own single-pair oracle run
+    H, W, n = 90, 160, 7
+    I0 = np.stack([synth.noisy_frame(H, W, t + 1, seq=t % 3) for t in range(n)])
+    I1 = np.stack([synth.noisy_frame(H, W, t, seq=t % 3) for t in range(n)])
+    I1[5] = I0[5]          # identical frames: zero flow
+    I0[6] = 17.0           # constant pair: den == 0 branch
+    I1[6] = 17.0
+    flow, iters = tvl1flow(dev(I0, cuda), dev(I1, cuda), nslots=3, return_iters=True, nscales=4)
+    fh, ih = tvl1flow_host(I0, I1, max_slots=4, return_iters=True, nscales=4)
+    o = OracleTvl1()
+    nexact = 0
+    for k in range(n):
+        u, it, _ = o.flow(I0[k], I1[k], nscales=4)
+        assert np.array_equal(iters[k], it), (k, iters[k], it)
+        assert np.array_equal(ih[k], it)
+        d = np.abs(flow[k].cpu().numpy() - u).max()
+        assert d <= FLOW_TOL, (k, d)
+        assert np.abs(fh[k] - u).max() <= FLOW_TOL
+        nexact += int(d == 0)
+    assert np.all(flow[6].cpu().numpy() == 0)
+    print("bit-exact pairs: %d / %d" % (nexact, n))
+
+
+def test_empty_batch_and_errors(cuda):
+    lib = _lib.lib()
+    e = torch.empty((0, 64, 64), device=cuda)
+    assert tvl1flow(e, e).shape == (0, 2, 64, 64)
+    with pytest.raises(ValueError):
+        tvl1flow(torch.zeros((1, 64, 64), device=cuda), torch.zeros((1, 64, 65), device=cuda))
+    with pytest.raises(RuntimeError):
+        tvl1flow(torch.zeros((1, 64, 64)), torch.zeros((1, 64, 64)))   # CPU tensor: no fallback
+
+
+def test_1080p_properties(cuda):
+    # full-size pair: symmetric inputs give mirrored flows (size-independent property) and
+    # the flow of (I, I) is exactly zero; iteration counts are reported for the bench.
+    H, W = 1080, 1920
+    I0, I1 = synth.noisy_frame(H, W, 1), synth.noisy_frame(H, W, 0)
+    pair0 = np.stack([I0, I0[:, ::-1].copy(), I0])
+    pair1 = np.stack([I1, I1[:, ::-1].copy(), I0])
+    flow, iters = tvl1flow(dev(pair0, cuda), dev(pair1, cuda), nslots=3, return_iters=True, nscales=5)
+    f = flow.cpu().numpy()
+    assert np.all(f[2] == 0)
+    assert np.isfinite(f).all()
+    # background moves by (1.5,-0.75): median flow from frame 1 to frame 0
+    assert abs(np.median(f[0, 0]) - 1.5) < 0.5 and abs(np.median(f[0, 1]) + 0.75) < 0.5
+    print("1080p iters (scale x warp):", iters[0].tolist())
