@@ -36,6 +36,7 @@ def _declare(lib):
     lib.f2f_tvl1_zoom_in_scaled.argtypes = [fp, fp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, vp]
     lib.f2f_tvl1_centered_gradient.argtypes = [fp, fp, fp, C.c_int, C.c_int, vp]
     lib.f2f_tvl1_normalize.argtypes = [fp, fp, fp, fp, C.c_int, C.c_int, vp, vp]
+    lib.f2f_selftest_division.argtypes = [C.c_ulonglong, C.POINTER(C.c_ulonglong)]
     lib.f2f_release.restype = None
 
 

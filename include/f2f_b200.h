@@ -118,6 +118,11 @@ int f2f_tvl1_normalize(const float *d_I0, const float *d_I1, float *d_I0n,
                        float *d_I1n, int nx, int ny, void *d_scratch8,
                        void *stream);                      /* tvl1flow_lib.c:314-348 */
 
+/* Compares the iteration kernel's in-line correctly-rounded division with IEEE
+ * division on n pseudo-random operand pairs in the ranges the solver produces;
+ * *h_mismatches receives the number of differing results (expected 0). */
+int f2f_selftest_division(unsigned long long n, unsigned long long *h_mismatches);
+
 /* Release every cached device allocation of the calling process. */
 void f2f_release(void);
 

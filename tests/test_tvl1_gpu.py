@@ -127,3 +127,12 @@ def test_1080p_properties(cuda):
     # background moves by (1.5,-0.75): median flow from frame 1 to frame 0
     assert abs(np.median(f[0, 0]) - 1.5) < 0.5 and abs(np.median(f[0, 1]) + 0.75) < 0.5
     print("1080p iters (scale x warp):", iters[0].tolist())
+
+
+def test_inline_division_is_ieee(cuda):
+    # the iteration kernel divides with a refined reciprocal + two residual corrections;
+    # it must agree bit-for-bit with IEEE division on the operand ranges of the solver
+    import ctypes as C
+    bad = C.c_ulonglong(123)
+    _lib.check(_lib.lib().f2f_selftest_division(1 << 30, C.byref(bad)), "selftest")
+    assert bad.value == 0
