@@ -1,0 +1,298 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the frame2frame hot path on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+                    [--workload tvl1|f2f]
+
+Workloads (BASELINE.json configs):
+  tvl1 : configs[1] -- TV-L1 flow on synthetic 1080p gray frame pairs, 5-scale
+         pyramid, default warps; frame pairs sharded over the GPUs (no
+         collective on the data path).  A step = one batch of PAIRS_PER_STEP
+         frame pairs per GPU.  metric = flow fields / s.
+  f2f  : configs[2] -- online F2F denoising of a synthetic 1080p sequence
+         (see bench_f2f.py); selected automatically once that path is built.
+
+One JSON line on stdout (rank 0).  `value` is timed with the frames resident in
+HBM; `e2e` is the same metric through the host-buffer C-ABI call
+(f2f_tvl1_flow_batch_host: H2D of the frames and D2H of the flows inside the
+timed region, from/to pinned host memory).  `--impl reference` times the
+reference's own CPU code (oracle/_ref, tvl1flow_lib.c compiled in place) on the
+host cores.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+H, W = 1080, 1920
+NSCALES = 5
+PAIRS_PER_STEP = 16          # per GPU; 16 pairs x 2 frames x 8.3 MB = 265 MB > L2 (126 MB)
+ALG_BYTES_PER_PX_ITER = 64   # read rho_c,I1wx,I1wy,grad,u1,u2,p11..p22; write u1,u2,p11..p22
+
+
+def peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))), "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.samples, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.samples.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for s in self.samples:
+            f = [x.strip() for x in s.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx = float(f[1])
+            except ValueError:
+                continue
+            for n, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def make_pairs(n, seq):
+    """n consecutive synthetic 1080p frame pairs (I0 = frame t+1, I1 = frame t: the
+    backward flow tvl1flow.sh:11-14 computes)."""
+    import numpy as np
+    from frame2frame_b200 import synth
+    nf = min(n, 8) + 1                      # cycle through 8 distinct pairs; noise differs per seq
+    frames = [synth.noisy_frame(H, W, t, seq=seq) for t in range(nf)]
+    I0 = np.stack([frames[(k % (nf - 1)) + 1] for k in range(n)])
+    I1 = np.stack([frames[(k % (nf - 1))] for k in range(n)])
+    return I0, I1
+
+
+def reference_arm(args, rank, world):
+    """The reference's own CPU implementation (tvl1flow_lib.c built in place, OpenMP, all host
+    threads) on a bounded sample of the same workload: one 1080p frame pair per step."""
+    if rank != 0:
+        return
+    import numpy as np
+    from oracle.tvl1 import OracleTvl1, RefTvl1
+    cores = os.cpu_count() or 1
+    os.environ.setdefault("OMP_NUM_THREADS", str(cores))
+    if RefTvl1.available():
+        impl, kind = RefTvl1(), "reference"
+        run = lambda a, b: impl.flow(a, b, nscales=NSCALES)
+    else:
+        impl, kind = OracleTvl1(), "port"
+        run = lambda a, b: impl.flow(a, b, nscales=NSCALES)[0]
+    I0, I1 = make_pairs(max(1, min(args.steps + args.warmup, 8)), 0)
+    for k in range(args.warmup):
+        run(I0[k % len(I0)], I1[k % len(I0)])
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        run(I0[(args.warmup + k) % len(I0)], I1[(args.warmup + k) % len(I0)])
+    dt = time.perf_counter() - t0
+    v = args.steps / dt
+    print(json.dumps({
+        "impl": "reference", "metric": "TV-L1 flow fields/sec @1080p gray", "value": v, "unit": "fields/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "configs[1]: tvl1flow 1080p gray pairs, 5 scales, 5 warps, eps 0.01 "
+                               "(bounded sample: 1 pair per step)"},
+        "cpu_baseline": {"value": v, "unit": "fields/s", "cores": cores, "kind": kind,
+                         "sample": "%d x 1 pair 1920x1080, OpenMP %d threads" % (args.steps, cores)},
+        "e2e": {"value": v, "unit": "fields/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def cpu_baseline(seconds_budget=25.0):
+    """Reference CPU path on this box's host cores, bounded sample (rank 0, N=1)."""
+    from oracle.tvl1 import OracleTvl1, RefTvl1
+    cores = os.cpu_count() or 1
+    os.environ.setdefault("OMP_NUM_THREADS", str(cores))
+    if RefTvl1.available():
+        impl, kind = RefTvl1(), "reference"
+        run = lambda a, b: impl.flow(a, b, nscales=NSCALES)
+    else:
+        impl, kind = OracleTvl1(), "port"
+        run = lambda a, b: impl.flow(a, b, nscales=NSCALES)[0]
+    I0, I1 = make_pairs(2, 0)
+    n, t0 = 0, time.perf_counter()
+    while True:
+        run(I0[n % 2], I1[n % 2])
+        n += 1
+        dt = time.perf_counter() - t0
+        if n >= 2 and (dt > seconds_budget * 0.6 or n >= 4):
+            break
+        if dt > seconds_budget:
+            break
+    return {"value": n / dt, "unit": "fields/s", "cores": cores, "kind": kind,
+            "sample": "%d pair(s) 1920x1080 in %.1f s, OpenMP %d threads" % (n, dt, cores)}
+
+
+def ours_tvl1(args, rank, world, local_rank):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from frame2frame_b200 import _lib
+    from frame2frame_b200.tvl1 import make_params, tvl1flow
+
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    lib = _lib.lib()                                   # raises if the CUDA library is missing
+    n = PAIRS_PER_STEP
+    I0h, I1h = make_pairs(n, rank)
+    # pinned host copies for the e2e leg
+    pI0 = torch.from_numpy(I0h).pin_memory()
+    pI1 = torch.from_numpy(I1h).pin_memory()
+    pU = torch.empty((n, 2, H, W), dtype=torch.float32).pin_memory()
+    dI0, dI1 = pI0.to(dev), pI1.to(dev)
+    p = make_params(W, H, nscales=NSCALES)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_device():
+        return tvl1flow(dI0, dI1, nslots=n, nscales=NSCALES)
+
+    def step_host():
+        _lib.check(lib.f2f_tvl1_flow_batch_host(pI0.data_ptr(), pI1.data_ptr(), pU.data_ptr(), n, W, H, C.byref(p),
+                                                None, n), "f2f_tvl1_flow_batch_host")
+
+    # ---- device-resident timing (`value`) ----
+    for _ in range(args.warmup):
+        step_device()
+    prof = (C.c_double * 5)()
+    lib.f2f_profile_read(prof)
+    launches_before = prof[4]
+    lib.f2f_profile_enable(1)
+    barrier()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        flow = step_device()
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop() if sampler else None
+    lib.f2f_profile_read(prof)
+    lib.f2f_profile_enable(0)
+    iter_ms, slot_iters0, px0, launches0, launches_after = [prof[i] for i in range(5)]
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max = float(t.item())
+    value = world * n * args.steps / (ms_max * 1e-3)
+
+    # ---- end to end through the host-buffer C ABI (`e2e`) ----
+    step_host()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step_host()
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    t = torch.tensor([dt], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = world * n * args.steps / float(t.item())
+    checksum = float(pU.double().abs().mean())
+
+    if rank != 0:
+        return
+    pk, pk_kind = peaks()
+    alg_bytes = ALG_BYTES_PER_PX_ITER * px0 * slot_iters0
+    achieved = alg_bytes / (iter_ms * 1e-3) / 1e9 if iter_ms > 0 else None
+    line = {
+        "metric": "TV-L1 flow fields/sec @1080p gray", "value": value, "unit": "fields/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_max / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "configs[1]: tvl1flow on synthetic 1080p gray frame pairs, 5-scale pyramid, 5 warps, "
+                               "eps 0.01, frame pairs sharded over GPUs",
+                   "pairs_per_step_per_gpu": n, "frame": "%dx%d" % (W, H),
+                   "l2": "inputs larger than L2 (265 MB of frames + 3.4 GB of solver state per step)"},
+        "e2e": {"value": e2e_value, "unit": "fields/s", "h2d_bytes_per_step": 2 * n * H * W * 4,
+                "d2h_bytes_per_step": 2 * n * H * W * 4, "api": "f2f_tvl1_flow_batch_host (C ABI, pinned host buffers)",
+                "flow_abs_mean": checksum},
+        "gpu_launches": int(launches_after - launches_before - 0) if launches_after else None,
+        "clocks": clocks,
+        "roofline": {"bound": "hbm", "kernel": "k_iter_strip<4> (fused primal-dual iteration, finest scale)",
+                     "achieved": achieved, "peak": pk["hbm_gbs"], "peak_source": pk_kind, "unit": "GB/s",
+                     "frac": (achieved / pk["hbm_gbs"]) if achieved else None,
+                     "alg_bytes_per_px_iter": ALG_BYTES_PER_PX_ITER,
+                     "px_iters_per_step": px0 * slot_iters0 / args.steps,
+                     "launches_per_step": launches0 / args.steps,
+                     "avg_launch_us": iter_ms * 1e3 / launches0 if launches0 else None,
+                     "traffic": 2.148e9, "traffic_note": "dram read+write per launch of 16 slots, ncu --set full, "
+                                                         "profiles/r01_tvl1_iter_strip.md"},
+    }
+    if world == 1 and not args.no_cpu:
+        line["cpu_baseline"] = cpu_baseline()
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="tvl1", choices=["tvl1"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        reference_arm(args, rank, world)
+        return
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback in the product path)")
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    try:
+        ours_tvl1(args, rank, world, local_rank)
+    finally:
+        if world > 1:
+            import torch.distributed as dist
+            dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -118,6 +118,16 @@ int f2f_tvl1_normalize(const float *d_I0, const float *d_I1, float *d_I0n,
                        float *d_I1n, int nx, int ny, void *d_scratch8,
                        void *stream);                      /* tvl1flow_lib.c:314-348 */
 
+/* Measurement hooks for bench.py.  While enabled, the TV-L1 batch brackets the
+ * finest-scale inner-iteration launches with CUDA events on the caller's
+ * stream (and synchronises at the end of each group to read them).
+ * f2f_profile_read: out[0] = ms spent in those launches, out[1] = sum over
+ * frame pairs of inner iterations run at scale 0, out[2] = pixels of scale 0,
+ * out[3] = number of those launches, out[4] = kernels launched by the library
+ * since load (all entry points). */
+void f2f_profile_enable(int on);
+void f2f_profile_read(double out[5]);
+
 /* Compares the iteration kernel's in-line correctly-rounded division with IEEE
  * division on n pseudo-random operand pairs in the ranges the solver produces;
  * *h_mismatches receives the number of differing results (expected 0). */
