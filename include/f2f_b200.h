@@ -118,6 +118,36 @@ int f2f_tvl1_normalize(const float *d_I0, const float *d_I1, float *d_I0n,
                        float *d_I1n, int nx, int ny, void *d_scratch8,
                        void *stream);                      /* tvl1flow_lib.c:314-348 */
 
+/* ------------------------------------------------- frame-to-frame step */
+
+/* Replaces WarpedLoss.warp + WarpedLoss.occlusion_mask (blind_denoising.py:49-113,
+ * lib/frame2frame/warped_loss.py:145-211) with one kernel.
+ *   d_x      [B,C,H,W] frame to warp (the previous frame)
+ *   d_flow   [B,2,H,W] flow, channel 0 = horizontal; the occlusion test uses
+ *            batch item 0's flow for every item and only mask[0,0] is dilated,
+ *            exactly as the reference code does (blind_denoising.py:92-103)
+ *   d_in_mask optional [B,C,H,W] multiplied into the mask (warped_loss.py:222-223)
+ *   d_warped [B,C,H,W] out: bilinear sample, zeros padding
+ *   d_valid  optional out: the mask warp() returns (1 where the sample of a
+ *            ones image is >= 0.9999, blind_denoising.py:73-76)
+ *   d_mask   optional out: valid * (1 - occluded), blind_denoising.py:112
+ *   align_corners: 0 = as run by the reference under torch >= 1.3
+ *            (grid_sample default), 1 = the convention its grid scaling assumes
+ *   occ_f64: 1 = float64 sum/compare of blind_denoising.py:88-94,
+ *            0 = float32 of warped_loss.py:184-190 */
+int f2f_warp_mask(const float *d_x, const float *d_flow, const float *d_in_mask,
+                  float *d_warped, float *d_valid, float *d_mask, int B, int C, int H,
+                  int W, int align_corners, int occ_f64, void *stream);
+/* WarpedLoss.occlusion_mask alone (blind_denoising.py:81-113). */
+int f2f_occlusion_mask(const float *d_flow, const float *d_old_mask, float *d_mask,
+                       int B, int C, int H, int W, int occ_f64, void *stream);
+/* Masked loss and its gradient wrt d_in in one pass; *d_loss (device double)
+ * is overwritten.  kind 0: sum|m*in-m*w| (blind_denoising.py:121);
+ * 1: mean (.)^2; 2: mean sqrt((.)^2+1e-6) (warped_loss.py:239-248).
+ * d_grad may be NULL. */
+int f2f_masked_loss(const float *d_in, const float *d_warped, const float *d_mask,
+                    float *d_grad, double *d_loss, size_t n, int kind, void *stream);
+
 /* Measurement hooks for bench.py.  While enabled, the TV-L1 batch brackets the
  * finest-scale inner-iteration launches with CUDA events on the caller's
  * stream (and synchronises at the end of each group to read them).
