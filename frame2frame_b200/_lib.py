@@ -40,6 +40,9 @@ def _declare(lib):
     lib.f2f_warp_mask.argtypes = [fp, fp, fp, fp, fp, fp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp]
     lib.f2f_occlusion_mask.argtypes = [fp, fp, fp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp]
     lib.f2f_masked_loss.argtypes = [fp, fp, fp, fp, vp, sz, C.c_int, vp]
+    lib.f2f_dncnn_prep_w64.argtypes = [fp, vp, C.c_int, vp]
+    lib.f2f_dncnn_conv64.argtypes = [vp, vp, vp, fp, fp, vp, C.c_int, C.c_int, vp]
+    lib.f2f_dncnn_dgrad64.argtypes = [vp, vp, vp, vp, fp, fp, fp, fp, vp, C.c_int, C.c_int, vp]
     lib.f2f_profile_enable.argtypes = [C.c_int]
     lib.f2f_profile_enable.restype = None
     lib.f2f_profile_read.argtypes = [C.POINTER(C.c_double)]

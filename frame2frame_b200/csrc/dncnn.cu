@@ -1,2 +1,409 @@
-// dncnn.cu -- placeholder translation unit (kernels land here next)
-namespace f2f { long g_dncnn_launches = 0; }
+// dncnn.cu -- DnCNN-17 (3x3 / 64-channel conv + BatchNorm + ReLU stack) forward
+// and backward for sm_100a.  Replaces the cuDNN/ATen calls behind
+// lib/frame2frame/dncnn/net.py:6-39 as driven by blind_denoising.py:211-230.
+//
+// The 64->64 convolutions are implicit GEMMs on the 5th-generation tensor cores:
+// tcgen05.mma (kind::f16, BF16 x BF16 -> FP32) issued by one thread per CTA,
+// accumulators in TMEM, weights staged once per CTA by the TMA engine
+// (cp.async.bulk), activations in NHWC BF16 (one pixel = 64 channels = 128 B).
+//
+// Shared-memory operand layout ("chunk-planar", no swizzle): a haloed 18x18
+// pixel tile is stored as 8 planes (one per 8-channel / 16-byte chunk) of
+// consecutive pixels.  In that layout a UMMA core matrix (8 rows x 16 B) is 8
+// horizontally adjacent pixels, so the A operand of filter tap (dy,dx) is the
+// SAME tile read through a descriptor whose start address is advanced by
+// ((dy+1)*18 + (dx+1)) * 16 bytes: nine taps, one tile, no im2col copies and no
+// swizzle-phase constraints.  The same planes read as an MN-major operand give
+// the pixel-contraction GEMM of the weight gradient.
+//
+// Train-mode BatchNorm needs the per-channel batch statistics of a layer's
+// whole output before it can be normalised, so conv(k) stores the
+// raw z_k (BF16) and reduces sum / sum-of-squares in its epilogue, and the
+// normalise + ReLU is applied by conv(k+1)'s operand producer while it stages
+// the tile -- no separate pass over the activations.
+//
+// CTA = 9 warps, persistent over 16x16-pixel tiles:
+//   warps 0-3  epilogue  (TMEM -> registers -> smem transpose -> coalesced stores + statistics)
+//   warps 4-7  producer  (global -> BN/ReLU -> chunk-planar smem, 3-stage ring)
+//   warp  8    MMA issuer (72 tcgen05.mma per tile into a double-buffered accumulator) + TMEM owner
+#include "f2f_common.cuh"
+#include "tc05.cuh"
+
+namespace f2f {
+
+long g_dncnn_launches = 0;
+
+namespace dn {
+
+using namespace tc05;
+typedef __nv_bfloat16 bf16;
+
+constexpr int TW = 16, TH = 16;              // output tile
+constexpr int HW = TW + 2, HH = TH + 2;      // with the 1-px halo of a 3x3 filter
+constexpr int HPIX = HW * HH;                // 324
+constexpr int CH_STRIDE = (HPIX + 1) * 16;   // bytes between 8-channel planes; odd multiple of 16 B: conflict-free staging
+constexpr int A_STAGE = 8 * CH_STRIDE;       // 41600
+constexpr int STAGES = 3;
+constexpr int B_TAP = 64 * 64 * 2;           // one tap's 64x64 BF16 weights
+constexpr int B_BYTES = 9 * B_TAP;           // 73728
+constexpr int EPI_ROW = 144;                 // 128 B of channels + 16 B pad (bank spread)
+constexpr int EPI_WARP = 32 * EPI_ROW;
+constexpr int EPI_BYTES = 4 * EPI_WARP;
+constexpr int OFF_B = 0;
+constexpr int OFF_A = OFF_B + B_BYTES;
+constexpr int OFF_EPI = OFF_A + STAGES * A_STAGE;
+constexpr int OFF_BAR = OFF_EPI + EPI_BYTES;
+constexpr int SMEM_BYTES = OFF_BAR + 256;
+constexpr int NTHREADS = 288;
+constexpr int TMEM_COLS = 256;               // 2 tile buffers x 2 halves x 64 fp32 columns
+
+enum Prologue { PRO_RAW = 0, PRO_BN_RELU = 1 };
+enum Epilogue { EPI_STORE = 0, EPI_STATS = 1, EPI_DGRAD_BN = 2, EPI_DGRAD_RELU = 3 };
+
+struct ConvArgs {
+    const bf16 *in;        // [H][W][64]
+    bf16 *out;             // [H][W][64]
+    const bf16 *wprep;     // [9 taps][8 k-chunks][64 n][8 k] BF16 = the smem image of B
+    const float *scale;    // prologue BN: a = relu(in*scale + shift), per input channel
+    const float *shift;
+    double *stats;         // [2][64] accumulators (EPI_STATS: sum z, sum z^2; EPI_DGRAD_BN: sum g, sum g*xhat)
+    const bf16 *zprev;     // EPI_DGRAD_*: pre-activation (BN) or activation (RELU) of the layer below
+    const float *p_scale;  // EPI_DGRAD_BN: BN of the layer below: y = z*p_scale + p_shift, xhat = (z - p_mean)*p_invstd
+    const float *p_shift;
+    const float *p_mean;
+    const float *p_invstd;
+    int H, W, tiles_x, tiles_y;
+};
+
+// ------------------------------------------------------------------ producer
+// Stages one haloed tile: 324 pixels x 8 chunks of 16 B.  Thread t owns chunk t%8 of pixels
+// t/8, t/8+16, ...: 8 consecutive lanes read one pixel's 128 B, a warp reads 4 adjacent pixels.
+template <int PRO>
+__device__ __forceinline__ void produce_tile(const ConvArgs &a, int tile, uint8_t *stage, int ptid, const float (&sc)[8],
+                                             const float (&sh)[8])
+{
+    const int ty0 = (tile / a.tiles_x) * TH - 1, tx0 = (tile % a.tiles_x) * TW - 1;
+    const int chunk = ptid & 7;
+    uint8_t *dst_plane = stage + chunk * CH_STRIDE;
+    constexpr int ROUNDS = (HPIX + 15) / 16;   // 21 rounds of 16 pixels (128 threads / 8 chunks)
+    constexpr int U = 7;
+    int pix = ptid >> 3;
+    int hy = pix / HW, hx = pix % HW;
+#pragma unroll 1
+    for (int r0 = 0; r0 < ROUNDS; r0 += U) {
+        uint4 v[U];
+        bool inb[U];
+        int px[U];
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            px[u] = pix;
+            const int gy = ty0 + hy, gx = tx0 + hx;
+            inb[u] = pix < HPIX && gy >= 0 && gy < a.H && gx >= 0 && gx < a.W;
+            v[u] = make_uint4(0, 0, 0, 0);
+            if (inb[u]) v[u] = __ldg(reinterpret_cast<const uint4 *>(a.in + ((size_t)gy * a.W + gx) * 64 + chunk * 8));
+            pix += 16;
+            hx += 16;
+            if (hx >= HW) { hx -= HW; hy += 1; }
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (px[u] < HPIX) {
+                uint4 o = v[u];
+                if (PRO == PRO_BN_RELU && inb[u]) {   // zero padding applies to the ACTIVATION: out-of-image stays 0
+                    uint32_t w[4] = {o.x, o.y, o.z, o.w};
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        const float2 f = unpack_bf16(w[j]);
+                        const float y0 = fmaxf(fmaf(f.x, sc[2 * j], sh[2 * j]), 0.0f);
+                        const float y1 = fmaxf(fmaf(f.y, sc[2 * j + 1], sh[2 * j + 1]), 0.0f);
+                        w[j] = pack_bf16(y0, y1);
+                    }
+                    o = make_uint4(w[0], w[1], w[2], w[3]);
+                }
+                *reinterpret_cast<uint4 *>(dst_plane + px[u] * 16) = o;
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------ epilogue
+// One warp, one 32-pixel quarter of a tile half: TMEM row -> BF16 -> smem transpose, per-channel
+// statistics from the rounded values, coalesced 512-B stores.
+template <int EPI>
+__device__ __forceinline__ void epilogue_half(const ConvArgs &a, uint32_t tmem_addr, uint8_t *stg, int lane, int warp,
+                                              int ty_base, int tx_base, float (&acc0)[2], float (&acc1)[2])
+{
+    // this thread's accumulator row m = 32*warp + lane  <->  pixel (tile row m/8, column m%8 of the half)
+    uint32_t r[32];
+    uint8_t *myrow = stg + lane * EPI_ROW;
+#pragma unroll
+    for (int part = 0; part < 2; part++) {
+        tmem_ld32(tmem_addr + part * 32, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            uint4 o;
+            o.x = pack_bf16(__uint_as_float(r[8 * j + 0]), __uint_as_float(r[8 * j + 1]));
+            o.y = pack_bf16(__uint_as_float(r[8 * j + 2]), __uint_as_float(r[8 * j + 3]));
+            o.z = pack_bf16(__uint_as_float(r[8 * j + 4]), __uint_as_float(r[8 * j + 5]));
+            o.w = pack_bf16(__uint_as_float(r[8 * j + 6]), __uint_as_float(r[8 * j + 7]));
+            *reinterpret_cast<uint4 *>(myrow + part * 64 + j * 16) = o;
+        }
+    }
+    __syncwarp();
+    // transposed phase: lane handles chunk (lane % 8) of pixels q = lane/8 + 4*i  (4 pixels = 512 contiguous bytes)
+    const int chunk = lane & 7;
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        const int q = (lane >> 3) + 4 * i;           // pixel index within the warp's 32
+        const int gy = ty_base + warp * 4 + (q >> 3), gx = tx_base + (q & 7);
+        uint4 o = *reinterpret_cast<const uint4 *>(stg + q * EPI_ROW + chunk * 16);
+        const bool inb = gy < a.H && gx < a.W;
+        if (EPI == EPI_DGRAD_BN || EPI == EPI_DGRAD_RELU) {
+            // ReLU mask of the layer below (and its BN-backward sums), net.py:16-18 backward
+            uint32_t w[4] = {o.x, o.y, o.z, o.w};
+            uint4 zz = make_uint4(0, 0, 0, 0);
+            if (inb) zz = __ldg(reinterpret_cast<const uint4 *>(a.zprev + ((size_t)gy * a.W + gx) * 64 + chunk * 8));
+            const uint32_t zw[4] = {zz.x, zz.y, zz.z, zz.w};
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                float2 g = unpack_bf16(w[j]);
+                const float2 z = unpack_bf16(zw[j]);
+                if (EPI == EPI_DGRAD_BN) {
+                    const int c = chunk * 8 + 2 * j;
+                    if (!(fmaf(z.x, a.p_scale[c], a.p_shift[c]) > 0.0f)) g.x = 0.0f;
+                    if (!(fmaf(z.y, a.p_scale[c + 1], a.p_shift[c + 1]) > 0.0f)) g.y = 0.0f;
+                } else {
+                    if (!(z.x > 0.0f)) g.x = 0.0f;
+                    if (!(z.y > 0.0f)) g.y = 0.0f;
+                }
+                w[j] = pack_bf16(g.x, g.y);
+            }
+            o = make_uint4(w[0], w[1], w[2], w[3]);
+            if (EPI == EPI_DGRAD_BN) *reinterpret_cast<uint4 *>(stg + q * EPI_ROW + chunk * 16) = o;   // for the sums below
+        }
+        if (inb) *reinterpret_cast<uint4 *>(a.out + ((size_t)gy * a.W + gx) * 64 + chunk * 8) = o;
+    }
+    if (EPI == EPI_STATS || EPI == EPI_DGRAD_BN) {
+        if (EPI == EPI_DGRAD_BN) __syncwarp();
+        // lane owns channels 2*lane, 2*lane+1; sums over the warp's 32 pixels (only those inside the image)
+        float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+        const int c = 2 * lane;
+        float m0 = 0.f, m1 = 0.f, i0 = 0.f, i1 = 0.f;
+        if (EPI == EPI_DGRAD_BN) { m0 = a.p_mean[c]; m1 = a.p_mean[c + 1]; i0 = a.p_invstd[c]; i1 = a.p_invstd[c + 1]; }
+#pragma unroll 8
+        for (int q = 0; q < 32; q++) {
+            const int gy = ty_base + warp * 4 + (q >> 3), gx = tx_base + (q & 7);
+            if (gy < a.H && gx < a.W) {
+                const float2 v = unpack_bf16(*reinterpret_cast<const uint32_t *>(stg + q * EPI_ROW + lane * 4));
+                if (EPI == EPI_STATS) {
+                    s0 += v.x; s1 += v.y;
+                    q0 = fmaf(v.x, v.x, q0); q1 = fmaf(v.y, v.y, q1);
+                } else {
+                    const float2 z = unpack_bf16(__ldg(reinterpret_cast<const uint32_t *>(a.zprev + ((size_t)gy * a.W + gx) * 64 + c)));
+                    s0 += v.x; s1 += v.y;
+                    q0 = fmaf(v.x, (z.x - m0) * i0, q0); q1 = fmaf(v.y, (z.y - m1) * i1, q1);
+                }
+            }
+        }
+        acc0[0] += s0; acc0[1] += s1; acc1[0] += q0; acc1[1] += q1;
+    }
+    __syncwarp();
+}
+
+// ------------------------------------------------------------------- kernel
+template <int PRO, int EPI>
+__global__ void __launch_bounds__(NTHREADS, 1) k_conv64(ConvArgs a)
+{
+    extern __shared__ __align__(1024) uint8_t smem[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int ntiles = a.tiles_x * a.tiles_y;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + OFF_BAR);
+    // barrier slots: full[3] @0, empty[3] @3, tfull[2] @6, tempty[2] @8, wbar @10; tmem base pointer @ +12
+    const uint32_t bar0 = smem_u32(bars);
+    auto BAR = [&](int i) { return bar0 + 8u * i; };
+    uint32_t *tmem_ptr = reinterpret_cast<uint32_t *>(bars + 12);
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; s++) { mbar_init(BAR(s), 128); mbar_init(BAR(3 + s), 1); }
+        for (int b = 0; b < 2; b++) { mbar_init(BAR(6 + b), 1); mbar_init(BAR(8 + b), 128); }
+        mbar_init(BAR(10), 1);
+        mbar_fence_init();
+    }
+    if (warp == 8) tmem_alloc(smem_u32(tmem_ptr), TMEM_COLS);
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem_base = *tmem_ptr;
+
+    if (warp >= 4 && warp < 8) {
+        // ===== producers =====
+        const int ptid = threadIdx.x - 128;
+        float sc[8], sh[8];
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            sc[j] = PRO == PRO_BN_RELU ? a.scale[(ptid & 7) * 8 + j] : 1.0f;
+            sh[j] = PRO == PRO_BN_RELU ? a.shift[(ptid & 7) * 8 + j] : 0.0f;
+        }
+        int it = 0;
+        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it++) {
+            const int s = it % STAGES;
+            const uint32_t ph = (it / STAGES) & 1;
+            mbar_wait(BAR(3 + s), ph ^ 1);                 // slot free (first pass returns immediately)
+            produce_tile<PRO>(a, tile, smem + OFF_A + s * A_STAGE, ptid, sc, sh);
+            fence_proxy_async();                           // st.shared -> visible to the tensor core's async proxy
+            mbar_arrive(BAR(s));
+        }
+    } else if (warp == 8) {
+        // ===== MMA issuer =====
+        if (lane == 0) {
+            // weights: one bulk copy by the TMA engine, resident for the whole kernel
+            mbar_arrive_expect_tx(BAR(10), B_BYTES);
+            for (int t = 0; t < 9; t++) bulk_g2s(smem_u32(smem + OFF_B + t * B_TAP), a.wprep + (size_t)t * 4096, B_TAP, BAR(10));
+            mbar_wait(BAR(10), 0);
+            constexpr uint32_t IDESC = idesc_bf16(128, 64, 0, 0);
+            int it = 0;
+            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it++) {
+                const int s = it % STAGES, b = it & 1;
+                mbar_wait(BAR(8 + b), ((it >> 1) & 1) ^ 1);   // accumulator buffer drained by the epilogue
+                mbar_wait(BAR(s), (it / STAGES) & 1);          // operand tile staged
+                fence_after_sync();
+                const uint32_t a_base = smem_u32(smem + OFF_A + s * A_STAGE);
+                const uint32_t b_base = smem_u32(smem + OFF_B);
+#pragma unroll 1
+                for (int tap = 0; tap < 9; tap++) {
+                    const int dy = tap / 3, dx = tap % 3;      // halo coordinates of the tap: (dy, dx) in 0..2
+                    const uint32_t a_tap = a_base + (uint32_t)(dy * HW + dx) * 16u;
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {              // K = 64 input channels = 4 x 16
+                        const uint64_t bd = smem_desc(b_base + tap * B_TAP + j * 2 * 1024, 1024, 128);
+#pragma unroll
+                        for (int h = 0; h < 2; h++) {          // left / right 8 columns of the 16-wide tile
+                            const uint64_t ad = smem_desc(a_tap + h * 8 * 16 + j * 2 * CH_STRIDE, CH_STRIDE, HW * 16);
+                            mma_ss(tmem_base + b * 128 + h * 64, ad, bd, IDESC, (tap | j) != 0);
+                        }
+                    }
+                }
+                mma_commit(BAR(3 + s));    // operand slot reusable once these MMAs have read it
+                mma_commit(BAR(6 + b));    // accumulators complete -> epilogue
+            }
+        }
+        __syncwarp();
+    } else {
+        // ===== epilogue =====
+        uint8_t *stg = smem + OFF_EPI + warp * EPI_WARP;
+        float acc0[2] = {0.f, 0.f}, acc1[2] = {0.f, 0.f};
+        double d0[2] = {0.0, 0.0}, d1[2] = {0.0, 0.0};
+        int it = 0;
+        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it++) {
+            const int b = it & 1;
+            const int ty = (tile / a.tiles_x) * TH, tx = (tile % a.tiles_x) * TW;
+            mbar_wait(BAR(6 + b), (it >> 1) & 1);
+            fence_after_sync();
+#pragma unroll 1
+            for (int h = 0; h < 2; h++)
+                epilogue_half<EPI>(a, tmem_base + ((uint32_t)(warp * 32) << 16) + b * 128 + h * 64, stg, lane, warp, ty,
+                                   tx + h * 8, acc0, acc1);
+            fence_before_sync();
+            mbar_arrive(BAR(8 + b));
+            if (EPI == EPI_STATS || EPI == EPI_DGRAD_BN) {   // fold the tile's FP32 partials into doubles
+                d0[0] += acc0[0]; d0[1] += acc0[1]; d1[0] += acc1[0]; d1[1] += acc1[1];
+                acc0[0] = acc0[1] = acc1[0] = acc1[1] = 0.f;
+            }
+        }
+        if ((EPI == EPI_STATS || EPI == EPI_DGRAD_BN) && a.stats) {
+            atomicAdd(a.stats + 2 * lane, d0[0]);
+            atomicAdd(a.stats + 2 * lane + 1, d0[1]);
+            atomicAdd(a.stats + 64 + 2 * lane, d1[0]);
+            atomicAdd(a.stats + 64 + 2 * lane + 1, d1[1]);
+        }
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (warp == 8) tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+// Weight layout transform: PyTorch conv weight [oc][ic][3][3] fp32 -> the smem image of B for
+//   forward (transpose = 0): B_tap[n = oc][k = ic] = w[oc][ic][tap]
+//   dgrad   (transpose = 1): B_tap[n = ic][k = oc] = w[oc][ic][8 - tap]   (flipped filter, transposed channels)
+// image order: [tap][k chunk of 8][n][8 k] bf16.
+__global__ void k_prep_w64(const float *__restrict__ w, bf16 *__restrict__ out, int transpose)
+{
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= 9 * 64 * 64) return;
+    const int kk = idx & 7, n = (idx >> 3) & 63, kc = (idx >> 9) & 7, tap = idx >> 12;
+    const int k = kc * 8 + kk;
+    float v;
+    if (!transpose) v = w[((size_t)n * 64 + k) * 9 + tap];
+    else v = w[((size_t)k * 64 + n) * 9 + (8 - tap)];
+    out[idx] = __float2bfloat16(v);
+}
+
+template <int PRO, int EPI>
+static int launch_conv64(const ConvArgs &a, cudaStream_t st)
+{
+    static bool configured = false;
+    if (!configured) {
+        F2F_CUDA_CHECK(cudaFuncSetAttribute(k_conv64<PRO, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        configured = true;
+    }
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int ntiles = a.tiles_x * a.tiles_y;
+    const int grid = ntiles < sms ? ntiles : sms;
+    k_conv64<PRO, EPI><<<grid, NTHREADS, SMEM_BYTES, st>>>(a);
+    g_dncnn_launches++;
+    F2F_LAUNCH_CHECK();
+    return F2F_OK;
+}
+
+}  // namespace dn
+}  // namespace f2f
+
+using namespace f2f;
+using namespace f2f::dn;
+
+extern "C" {
+
+int f2f_dncnn_prep_w64(const float *d_w, void *d_wprep, int transpose, void *stream)
+{
+    if (!d_w || !d_wprep) { set_error("f2f_dncnn_prep_w64: bad arguments"); return F2F_EINVAL; }
+    k_prep_w64<<<cdiv(9 * 64 * 64, 256), 256, 0, (cudaStream_t)stream>>>(d_w, (bf16 *)d_wprep, transpose);
+    g_dncnn_launches++;
+    F2F_LAUNCH_CHECK();
+    return F2F_OK;
+}
+
+int f2f_dncnn_conv64(const void *d_in, void *d_out, const void *d_wprep, const float *d_scale, const float *d_shift,
+                     double *d_stats, int H, int W, void *stream)
+{
+    if (!d_in || !d_out || !d_wprep || H < 1 || W < 1) { set_error("f2f_dncnn_conv64: bad arguments"); return F2F_EINVAL; }
+    ConvArgs a = {};
+    a.in = (const bf16 *)d_in; a.out = (bf16 *)d_out; a.wprep = (const bf16 *)d_wprep;
+    a.scale = d_scale; a.shift = d_shift; a.stats = d_stats;
+    a.H = H; a.W = W; a.tiles_x = cdiv(W, TW); a.tiles_y = cdiv(H, TH);
+    cudaStream_t st = (cudaStream_t)stream;
+    const bool bn = d_scale != nullptr;
+    if (bn && d_stats) return launch_conv64<PRO_BN_RELU, EPI_STATS>(a, st);
+    if (bn) return launch_conv64<PRO_BN_RELU, EPI_STORE>(a, st);
+    if (d_stats) return launch_conv64<PRO_RAW, EPI_STATS>(a, st);
+    return launch_conv64<PRO_RAW, EPI_STORE>(a, st);
+}
+
+int f2f_dncnn_dgrad64(const void *d_dz, void *d_gout, const void *d_wprep_t, const void *d_zprev, const float *d_pscale,
+                      const float *d_pshift, const float *d_pmean, const float *d_pinvstd, double *d_stats, int H, int W,
+                      void *stream)
+{
+    if (!d_dz || !d_gout || !d_wprep_t || !d_zprev || H < 1 || W < 1) { set_error("f2f_dncnn_dgrad64: bad arguments"); return F2F_EINVAL; }
+    ConvArgs a = {};
+    a.in = (const bf16 *)d_dz; a.out = (bf16 *)d_gout; a.wprep = (const bf16 *)d_wprep_t;
+    a.zprev = (const bf16 *)d_zprev; a.p_scale = d_pscale; a.p_shift = d_pshift; a.p_mean = d_pmean; a.p_invstd = d_pinvstd;
+    a.stats = d_stats;
+    a.H = H; a.W = W; a.tiles_x = cdiv(W, TW); a.tiles_y = cdiv(H, TH);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (d_pscale) return launch_conv64<PRO_RAW, EPI_DGRAD_BN>(a, st);
+    return launch_conv64<PRO_RAW, EPI_DGRAD_RELU>(a, st);
+}
+
+}  // extern "C"

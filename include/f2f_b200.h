@@ -148,6 +148,33 @@ int f2f_occlusion_mask(const float *d_flow, const float *d_old_mask, float *d_ma
 int f2f_masked_loss(const float *d_in, const float *d_warped, const float *d_mask,
                     float *d_grad, double *d_loss, size_t n, int kind, void *stream);
 
+/* ------------------------------------------------------------------ DnCNN */
+/* Layer-level entry points of the 17-layer DnCNN (lib/frame2frame/dncnn/net.py:6-39).
+ * Activations are NHWC BF16 ([H][W][64], one pixel = 128 B); B = 1 as in the
+ * reference's frame loop (blind_denoising.py:187-230). */
+
+/* conv weight [64][64][3][3] FP32 (PyTorch layout, net.py:16) -> BF16 operand image
+ * [9 taps][8][64][8] (147456 B) for the forward (transpose=0) or the input-gradient
+ * (transpose=1: flipped taps, transposed channels) tensor-core convolution. */
+int f2f_dncnn_prep_w64(const float *d_w, void *d_wprep, int transpose, void *stream);
+
+/* out = conv3x3(act(in)), 64->64, zero padding 1, no bias (net.py:16).
+ *   act = identity if d_scale == NULL, else relu(in*scale[c] + shift[c]): the
+ *   BatchNorm+ReLU of the layer below (net.py:17-18) folded into operand staging.
+ *   d_stats (optional, 128 doubles, accumulated into): per-channel sum and sum of
+ *   squares of the stored BF16 outputs = train-mode batch statistics. */
+int f2f_dncnn_conv64(const void *d_in, void *d_out, const void *d_wprep, const float *d_scale,
+                     const float *d_shift, double *d_stats, int H, int W, void *stream);
+
+/* Input gradient of a 64->64 conv fused with the backward of the ReLU (and BatchNorm
+ * sums) below it: g = conv3x3(dz, W^T flipped) masked by the layer below's ReLU.
+ *   d_zprev: with BN (d_pscale != NULL) the pre-BN output z of the layer below, mask is
+ *   z*pscale+pshift > 0 and d_stats accumulates sum g and sum g*xhat (xhat = (z-pmean)*pinvstd);
+ *   without BN (layer 0) its post-ReLU activation, mask is > 0. */
+int f2f_dncnn_dgrad64(const void *d_dz, void *d_gout, const void *d_wprep_t, const void *d_zprev,
+                      const float *d_pscale, const float *d_pshift, const float *d_pmean,
+                      const float *d_pinvstd, double *d_stats, int H, int W, void *stream);
+
 /* Measurement hooks for bench.py.  While enabled, the TV-L1 batch brackets the
  * finest-scale inner-iteration launches with CUDA events on the caller's
  * stream (and synchronises at the end of each group to read them).
