@@ -43,6 +43,18 @@ def _declare(lib):
     lib.f2f_dncnn_prep_w64.argtypes = [fp, vp, C.c_int, vp]
     lib.f2f_dncnn_conv64.argtypes = [vp, vp, vp, fp, fp, vp, C.c_int, C.c_int, vp]
     lib.f2f_dncnn_dgrad64.argtypes = [vp, vp, vp, vp, fp, fp, fp, fp, vp, C.c_int, C.c_int, vp]
+    lib.f2f_dncnn_wgrad64.argtypes = [vp, fp, vp, vp, fp, fp, fp, C.c_int, C.c_int, C.c_int, vp]
+    lib.f2f_dncnn_param_count.restype = sz
+    lib.f2f_dncnn_workspace_bytes.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int]
+    lib.f2f_dncnn_workspace_bytes.restype = sz
+    lib.f2f_dncnn_workspace_layout.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(sz)]
+    lib.f2f_dncnn_workspace_layout.restype = None
+    lib.f2f_dncnn_set_debug_dump.argtypes = [vp]
+    lib.f2f_dncnn_set_debug_dump.restype = None
+    lib.f2f_dncnn_forward.argtypes = [fp, fp, vp, fp, fp, vp, sz, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp]
+    lib.f2f_dncnn_backward.argtypes = [fp, fp, fp, vp, sz, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp]
+    lib.f2f_adam_step.argtypes = [fp, fp, fp, fp, sz, C.c_longlong, C.c_float, C.c_float, C.c_float, C.c_float,
+                                  C.c_float, vp]
     lib.f2f_profile_enable.argtypes = [C.c_int]
     lib.f2f_profile_enable.restype = None
     lib.f2f_profile_read.argtypes = [C.POINTER(C.c_double)]

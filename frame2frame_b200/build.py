@@ -27,6 +27,7 @@ UNITS = {
     "tvl1.cu": ["-fmad=false"],
     "f2f_step.cu": ["-fmad=false"],
     "dncnn.cu": [],
+    "dncnn_net.cu": [],
 }
 
 

@@ -175,6 +175,57 @@ int f2f_dncnn_dgrad64(const void *d_dz, void *d_gout, const void *d_wprep_t, con
                       const float *d_pscale, const float *d_pshift, const float *d_pmean,
                       const float *d_pinvstd, double *d_stats, int H, int W, void *stream);
 
+/* Weight gradient of a 64->64 conv (tcgen05, pixels as the contraction) fused with the
+ * BatchNorm backward of the layer: dz = A*g + B*z + C per channel is formed while the operand
+ * is staged and written back over d_g (so f2f_dncnn_dgrad64 can consume it next).
+ *   d_act    : the layer's input, z of the layer below (d_coef_in = its 448-float coefficient
+ *              block: scale[64], shift[64], mean[64], invstd[64], A[64], B[64], C[64]; BN+ReLU
+ *              applied on load) or a post-ReLU activation (d_coef_in = NULL)
+ *   d_g, d_z : masked output gradient (in) / dz (out), and the layer's pre-BN output
+ *   d_coef   : the layer's own coefficient block (A, B, C used)
+ *   d_partial: scratch, 148 * 49152 floats; d_dw: [64][64][3][3] FP32 (PyTorch layout). */
+int f2f_dncnn_wgrad64(const void *d_act, const float *d_coef_in, void *d_g, const void *d_z,
+                      const float *d_coef, float *d_partial, float *d_dw, int H, int W,
+                      int accumulate, void *stream);
+
+/* Whole network.  d_params / d_grads: flat FP32 vector in DnCNN.state_dict() order (conv0.w,
+ * then conv_k.w, bn_k.weight, bn_k.bias for k = 1..15, conv16.w; f2f_dncnn_param_count() =
+ * 556032 floats, channels = 1).  d_bn_running: [15][2][64] running mean / var; d_nbt: [15]
+ * num_batches_tracked (int64) or NULL.  d_x, d_y: [B][H][W] FP32.
+ *   train = 1: model.train() forward (blind_denoising.py:212-218) -- batch statistics over
+ *              B*H*W, running stats updated (momentum 0.1, unbiased variance), activations kept
+ *              in the workspace for f2f_dncnn_backward;
+ *   train = 0: model.eval() forward (blind_denoising.py:226-230);
+ *   residual : 0 = y is the noise estimate (the paper script's dncnn.models.DnCNN),
+ *              1 = y = x - noise (lib/frame2frame/dncnn/net.py:31). */
+size_t f2f_dncnn_param_count(void);
+size_t f2f_dncnn_workspace_bytes(int B, int H, int W, int train);
+/* Byte offsets inside the workspace, for layer-by-layer parity tests: out[0] saved input x
+ * (FP32), out[1] a_0 (NHWC BF16), out[2] z_1 (z_k at out[2] + (k-1)*out[3] in train mode, at
+ * out[2] + (k&1)*out[3] in eval mode), out[3] bytes of one activation, out[4], out[5] the two
+ * gradient buffers, out[6] coefficient blocks (15 x 448 floats), out[7] forward batch sums
+ * (15 x 128 doubles). */
+void f2f_dncnn_workspace_layout(int B, int H, int W, int train, size_t out[8]);
+/* Test hook: when d_buf != NULL, f2f_dncnn_backward copies its intermediate gradients into it
+ * (31 slots of out[3] bytes: slot 2(k-1) = masked gradient g_k entering layer k's BatchNorm
+ * backward, slot 2(k-1)+1 = dz_k, slot 30 = g_0), so each backward kernel can be checked against
+ * the reference formula on its own inputs.  NULL switches it off. */
+void f2f_dncnn_set_debug_dump(void *d_buf);
+int f2f_dncnn_forward(const float *d_params, float *d_bn_running, long long *d_nbt,
+                      const float *d_x, float *d_y, void *d_ws, size_t ws_bytes, int B, int H,
+                      int W, int train, int residual, void *stream);
+/* Gradient of a scalar loss wrt every parameter given d_dy = dL/dy of the last train-mode
+ * forward on the same workspace (loss.backward(), blind_denoising.py:221).  d_grads is
+ * overwritten (accumulate = 0) or added to (accumulate = 1). */
+int f2f_dncnn_backward(const float *d_params, float *d_grads, const float *d_dy, void *d_ws,
+                       size_t ws_bytes, int B, int H, int W, int residual, int accumulate,
+                       void *stream);
+/* torch.optim.Adam step (amsgrad = False, weight decay added to the gradient) on one flat
+ * tensor; `step` counts from 1 (blind_denoising.py:163-165, 222). */
+int f2f_adam_step(float *d_p, const float *d_g, float *d_m, float *d_v, size_t n,
+                  long long step, float lr, float beta1, float beta2, float eps,
+                  float weight_decay, void *stream);
+
 /* Measurement hooks for bench.py.  While enabled, the TV-L1 batch brackets the
  * finest-scale inner-iteration launches with CUDA events on the caller's
  * stream (and synchronises at the end of each group to read them).

@@ -19,7 +19,7 @@ print("iters pair0:", iters[0].tolist(), "sum per scale", iters[0].sum(1).tolist
 P = [1920*1080, 960*540, 480*270, 240*135, 120*68]
 pxit = sum(P[s] * iters[:, s].sum() for s in range(NS)) / n
 print("px-iter per field: %.1f M" % (pxit / 1e6))
-for rep in range(3):
+for rep in range(int(os.environ.get('REPS', '3'))):
     e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
     e0.record()
     flow = tvl1flow(I0, I1, nslots=slots, nscales=NS)
