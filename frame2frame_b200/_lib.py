@@ -55,6 +55,8 @@ def _declare(lib):
     lib.f2f_dncnn_backward.argtypes = [fp, fp, fp, vp, sz, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp]
     lib.f2f_adam_step.argtypes = [fp, fp, fp, fp, sz, C.c_longlong, C.c_float, C.c_float, C.c_float, C.c_float,
                                   C.c_float, vp]
+    lib.f2f_step_train.argtypes = [fp, fp, fp, fp, fp, vp, fp, fp, fp, fp, fp, vp, vp, sz, C.c_int, C.c_int, C.c_int,
+                                   C.c_longlong, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, vp]
     lib.f2f_profile_enable.argtypes = [C.c_int]
     lib.f2f_profile_enable.restype = None
     lib.f2f_profile_read.argtypes = [C.POINTER(C.c_double)]

@@ -1,0 +1,209 @@
+"""Model-blind video denoising by frame-to-frame fine-tuning -- the reference's
+``blind_denoising.py`` (CLI flags :264-288, ``blind_denoising(**args)`` :125-259, ``psnr``
+:36-41) on B200.
+
+Same flags, same inputs (frames ``--input %03d.png``/``.tiff``, flows ``--flow %03d.flo`` from
+frame i to frame i-1, reference frames ``--ref``, DnCNN-S-25 ``--network`` state dict with the
+``module.`` prefix), same outputs (denoised frames, one PSNR per line in ``--output_psnr``,
+``torch.save([model, optimizer])`` to ``--output_network``).  Underneath, every inner iteration
+``out = curr - model(curr); loss = WarpedLoss(out, prev, flow); backward; Adam`` is ONE call into
+libf2f_b200.so (f2f_step_train), the warp / validity / occlusion mask is computed once per frame
+instead of once per iteration on the host, and nothing runs on the CPU but file I/O.
+
+``OnlineF2F`` is the engine (frames and flows as tensors); ``blind_denoising()`` wraps it with
+the reference's file handling.  ``--flow`` may be omitted: the backward flow is then computed on
+the device by the TV-L1 kernels (what tvl1flow.sh:11-14 does in a separate process).
+"""
+import argparse
+import os
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from ._lib import check, lib
+from .dncnn import Adam, DnCNN
+from .tvl1 import read_flo, tvl1flow
+from .warped_loss import WarpedLoss, warp_mask
+
+LR, WEIGHT_DECAY, BETAS, EPS = 5e-5, 0.00001, (0.9, 0.999), 1e-08   # blind_denoising.py:158-165
+
+
+def psnr(img1, img2, peak=1):
+    """blind_denoising.py:36-41 (img2 is NOT clipped)."""
+    x = (np.array(img1).squeeze() - np.array(img2).squeeze()).flatten()
+    return 10 * np.log10(peak ** 2 / np.mean(x ** 2))
+
+
+def load_network(model_fn, device):
+    """blind_denoising.py:142-147: DnCNN(channels=1, num_of_layers=17) in DataParallel([0]) + state dict.
+    Accepts a torch ``.pth`` state dict or an ``.npz`` of arrays with the same keys."""
+    net = DnCNN(channels=1, num_of_layers=17, residual=False)      # the paper script's DnCNN returns the noise
+    model = nn.DataParallel(net, device_ids=[device.index or 0]).to(device)
+    if model_fn.endswith(".npz"):
+        sd = {k: torch.from_numpy(np.asarray(v, dtype=np.float32 if v.dtype.kind == "f" else v.dtype))
+              for k, v in np.load(model_fn).items()}
+    else:
+        sd = torch.load(model_fn, map_location="cpu")
+    if not any(k.startswith("module.") for k in sd):
+        sd = {"module." + k: v for k, v in sd.items()}
+    model.load_state_dict(sd)
+    return model
+
+
+class OnlineF2F:
+    """The per-frame body of blind_denoising.py:187-256 with everything resident on the device."""
+
+    def __init__(self, model, optimizer=None, align_corners=False):
+        self.model = model
+        self.net = model.module if isinstance(model, nn.DataParallel) else model
+        self.dev = self.net.flat_params.device
+        self.criterion = WarpedLoss(align_corners=align_corners).cuda(self.dev)
+        self.optimizer = optimizer or Adam(model.parameters(), lr=LR, betas=BETAS, eps=EPS, weight_decay=WEIGHT_DECAY,
+                                           amsgrad=False)
+        self._scratch = None
+
+    def _buffers(self, H, W):
+        if self._scratch is None or self._scratch[0] != (H, W):
+            mk = lambda: torch.empty((1, 1, H, W), dtype=torch.float32, device=self.dev)
+            self._scratch = ((H, W), mk(), mk(), torch.zeros((), dtype=torch.float64, device=self.dev))
+        return self._scratch[1:]
+
+    def finetune(self, curr, prev, flow, iters=20, losses=None):
+        """blind_denoising.py:211-222.  curr, prev: [1,1,H,W] in [0,1]; flow [1,2,H,W] (frame i -> i-1)."""
+        net = self.net
+        curr = curr.to(self.dev, torch.float32).contiguous()
+        _, _, H, W = curr.shape
+        self.model.train()
+        warped, mask = self.criterion.precompute(prev, flow)          # once per frame
+        out, dout, loss = self._buffers(H, W)
+        st, group = self.optimizer.fused_state(net)
+        ws = net._ws_train.get(1, H, W, True, self.dev)
+        b1, b2 = group["betas"]
+        stream = torch.cuda.current_stream().cuda_stream
+        with torch.cuda.device(self.dev):
+            for _ in range(iters):
+                check(lib().f2f_step_train(net.flat_params.data_ptr(), net.flat_grads.data_ptr(), st["exp_avg"].data_ptr(),
+                                           st["exp_avg_sq"].data_ptr(), net._running.data_ptr(), net._nbt.data_ptr(),
+                                           curr.data_ptr(), warped.data_ptr(), mask.data_ptr(), out.data_ptr(),
+                                           dout.data_ptr(), loss.data_ptr(), ws.data_ptr(), ws.numel(), H, W,
+                                           self.criterion.KIND, st["step"] + 1, group["lr"], b1, b2, group["eps"],
+                                           group["weight_decay"], stream), "f2f_step_train")
+                self.optimizer.advance()
+                if losses is not None:
+                    losses.append(float(loss.item()))
+        net._fwd_id += 1
+        net._attach_grads()
+
+    def denoise(self, curr):
+        """blind_denoising.py:226-230: eval-mode ``curr - model(curr)``."""
+        self.model.eval()
+        with torch.no_grad():
+            x = curr.to(self.dev, torch.float32).contiguous()
+            res = self.net.residual
+            self.net.residual = True
+            try:
+                return self.model(x)
+            finally:
+                self.net.residual = res
+
+    def step_frame(self, curr, prev, flow=None, iters=20, losses=None, flow_kw=None):
+        """Fine-tune on (curr, prev) and return the denoised curr.  flow=None: TV-L1 backward flow
+        (I0 = curr, I1 = prev, on 0..255 values like tvl1flow.sh:11-14) computed on the device."""
+        if flow is None:
+            flow = tvl1flow(curr[0, 0].to(self.dev) * 255.0, prev[0, 0].to(self.dev) * 255.0, **(flow_kw or {}))[None]
+        self.finetune(curr, prev, flow, iters, losses)
+        return self.denoise(curr)
+
+
+# ------------------------------------------------------------------ file handling
+def _is_tiff(path):
+    return path[-4:] == "tiff" or path[-3:] == "tif"
+
+
+def imread_gray(path):
+    """skimage.io.imread(path, as_gray=True) for 8-bit gray PNGs / tifffile.imread for TIFFs
+    (blind_denoising.py:170-174): ndarray [H,W]; colour images use the .2125/.7154/.0721 luma
+    skimage applies and come back in [0,1] like skimage does."""
+    from PIL import Image
+    im = Image.open(path)
+    if _is_tiff(path):
+        return np.array(im)
+    a = np.array(im)
+    if a.ndim == 3:
+        a = a[..., :3].astype(np.float64) / 255.0
+        return a @ np.array([0.2125, 0.7154, 0.0721])
+    return a
+
+
+def imsave(path, arr):
+    from PIL import Image
+    Image.fromarray(arr).save(path)
+
+
+def _to_batch(im):
+    """blind_denoising.py:177-180: [H,W] -> [1,1,H,W] / 255."""
+    if len(im.shape) < 4:
+        im = np.expand_dims(np.expand_dims(im, 0), 0)
+        im = im / 255.
+    return im
+
+
+def blind_denoising(**args):
+    """Main function (blind_denoising.py:125-259).  args: the CLI parameters below."""
+    dev = torch.device("cuda", int(args.get("gpu", 0) or 0))
+    model_fn = args["network"]
+    if not os.path.isabs(model_fn):
+        model_fn = os.path.join(os.path.abspath(os.path.dirname(__file__)), model_fn)
+    print("Loading model a pre-trained DnCNN\n")
+    model = load_network(model_fn, dev)
+    engine = OnlineF2F(model, align_corners=bool(args.get("align_corners", False)))
+
+    prev = torch.Tensor(_to_batch(imread_gray(args["input"] % (args["first"])))).to(dev)
+    plot_psnr = open(args["output_psnr"], "w")
+    for i in range(args["first"] + 1, args["last"] + 1):
+        print(i)
+        curr = torch.FloatTensor(_to_batch(imread_gray(args["input"] % (i)))).to(dev)
+        flow = None
+        if args.get("flow"):
+            flow = torch.Tensor(np.expand_dims(read_flo(args["flow"] % (i)), 0)).permute(0, 3, 1, 2)
+        den = engine.step_frame(curr, prev, flow, iters=args["iter"])
+        den_np = np.array(den.cpu())
+        if _is_tiff(args["ref"]):
+            imsave(args["output"] % (i), np.squeeze(255. * den_np).astype(np.float32))
+        else:
+            imsave(args["output"] % (i), np.squeeze(255. * np.clip(den_np, 0., 1.)).astype(np.uint8))
+        ref = _to_batch(imread_gray(args["ref"] % (i)))
+        quant = psnr(ref, den_np)
+        plot_psnr.write(str(quant) + "\n")
+        print(quant)
+        prev = curr
+    torch.save([model, engine.optimizer], args["output_network"])
+    plot_psnr.close()
+
+
+def main(argv=None):
+    parser = argparse.ArgumentParser(description="Blind_denoising")
+    parser.add_argument("--input", type=str, default="", help="path to input frames (C type)")
+    parser.add_argument("--ref", type=str, default="", help="path to reference frames (C type), against which the psnr is going to be computed")
+    parser.add_argument("--flow", type=str, default="", help="path to optical flow (C type); empty = TV-L1 on the device")
+    parser.add_argument("--output", type=str, default="./%03d.png", help="path to output image (C type)")
+    parser.add_argument("--output_psnr", type=str, default="plot_psnr.txt", help="path to output psnr")
+    parser.add_argument("--output_network", type=str, default="final.pth", help="path to output network")
+    parser.add_argument("--first", type=int, default=1, help="index first frame")
+    parser.add_argument("--last", type=int, default=300, help="index last frame")
+    parser.add_argument("--iter", type=int, default=20, help="number of time the learning is done on a given frame")
+    parser.add_argument("--network", type=str, default="dncnn/logs/DnCNN-S-25/net.pth", help="path to the network")
+    parser.add_argument("--gpu", type=int, default=0, help="(added) CUDA device index")
+    parser.add_argument("--align_corners", action="store_true", help="(added) sample with align_corners=True")
+    argspar = parser.parse_args(argv)
+    print("\n### Model-blind Video Denoising Via Frame-to-frame Training ###")
+    print("> Parameters:")
+    for p, v in zip(argspar.__dict__.keys(), argspar.__dict__.values()):
+        print("\t{}: {}".format(p, v))
+    print("\n")
+    blind_denoising(**vars(argspar))
+
+
+if __name__ == "__main__":
+    main()

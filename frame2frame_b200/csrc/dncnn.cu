@@ -22,10 +22,12 @@
 // normalise + ReLU is applied by conv(k+1)'s operand producer while it stages
 // the tile -- no separate pass over the activations.
 //
-// CTA = 9 warps, persistent over 16x16-pixel tiles:
-//   warps 0-3  epilogue  (TMEM -> registers -> smem transpose -> coalesced stores + statistics)
-//   warps 4-7  producer  (global -> BN/ReLU -> chunk-planar smem, 3-stage ring)
-//   warp  8    MMA issuer (72 tcgen05.mma per tile into a double-buffered accumulator) + TMEM owner
+// CTA = 13 warps, persistent over 16x16-pixel tiles:
+//   warps 0-3   epilogue  (TMEM -> registers -> smem transpose -> coalesced stores + statistics)
+//   warps 4-11  producers (global -> BN/ReLU -> chunk-planar smem, 3-stage ring): two groups of four
+//               warps take alternate tiles, each with the whole haloed tile's loads in flight at
+//               once (the layer is within ~20% of being HBM-bound, so bytes in flight matter)
+//   warp  12    MMA issuer (72 tcgen05.mma per tile into a double-buffered accumulator) + TMEM owner
 #include "f2f_common.cuh"
 #include "tc05.cuh"
 
@@ -54,7 +56,8 @@ constexpr int OFF_A = OFF_B + B_BYTES;
 constexpr int OFF_EPI = OFF_A + STAGES * A_STAGE;
 constexpr int OFF_BAR = OFF_EPI + EPI_BYTES;
 constexpr int SMEM_BYTES = OFF_BAR + 256;
-constexpr int NTHREADS = 288;
+constexpr int NTHREADS = 416;
+constexpr int MMA_WARP = 12;
 constexpr int TMEM_COLS = 256;               // 2 tile buffers x 2 halves x 64 fp32 columns
 
 enum Prologue { PRO_RAW = 0, PRO_BN_RELU = 1 };
@@ -76,8 +79,9 @@ struct ConvArgs {
 };
 
 // ------------------------------------------------------------------ producer
-// Stages one haloed tile: 324 pixels x 8 chunks of 16 B.  Thread t owns chunk t%8 of pixels
-// t/8, t/8+16, ...: 8 consecutive lanes read one pixel's 128 B, a warp reads 4 adjacent pixels.
+// Stages one haloed tile: 324 pixels x 8 chunks of 16 B.  Thread t of the 128-thread group owns
+// chunk t%8 of pixels t/8, t/8+16, ...: 8 consecutive lanes read one pixel's 128 B, a warp reads
+// 4 adjacent pixels.  All 21 loads of a thread are issued before the first is consumed.
 template <int PRO>
 __device__ __forceinline__ void produce_tile(const ConvArgs &a, int tile, uint8_t *stage, int ptid, const float (&sc)[8],
                                              const float (&sh)[8])
@@ -86,58 +90,77 @@ __device__ __forceinline__ void produce_tile(const ConvArgs &a, int tile, uint8_
     const int chunk = ptid & 7;
     uint8_t *dst_plane = stage + chunk * CH_STRIDE;
     constexpr int ROUNDS = (HPIX + 15) / 16;   // 21 rounds of 16 pixels (128 threads / 8 chunks)
-    constexpr int U = 7;
-    int pix = ptid >> 3;
-    int hy = pix / HW, hx = pix % HW;
-#pragma unroll 1
-    for (int r0 = 0; r0 < ROUNDS; r0 += U) {
-        uint4 v[U];
-        bool inb[U];
-        int px[U];
+    const int pix0 = ptid >> 3;
+    uint4 v[ROUNDS];
+    uint32_t inb = 0;
+    {
+        int hy = pix0 / HW, hx = pix0 % HW;
 #pragma unroll
-        for (int u = 0; u < U; u++) {
-            px[u] = pix;
+        for (int u = 0; u < ROUNDS; u++) {
             const int gy = ty0 + hy, gx = tx0 + hx;
-            inb[u] = pix < HPIX && gy >= 0 && gy < a.H && gx >= 0 && gx < a.W;
+            const bool ok = pix0 + 16 * u < HPIX && gy >= 0 && gy < a.H && gx >= 0 && gx < a.W;
             v[u] = make_uint4(0, 0, 0, 0);
-            if (inb[u]) v[u] = __ldg(reinterpret_cast<const uint4 *>(a.in + ((size_t)gy * a.W + gx) * 64 + chunk * 8));
-            pix += 16;
+            if (ok) {
+                v[u] = __ldg(reinterpret_cast<const uint4 *>(a.in + ((size_t)gy * a.W + gx) * 64 + chunk * 8));
+                inb |= 1u << u;
+            }
             hx += 16;
             if (hx >= HW) { hx -= HW; hy += 1; }
         }
+    }
 #pragma unroll
-        for (int u = 0; u < U; u++) {
-            if (px[u] < HPIX) {
-                uint4 o = v[u];
-                if (PRO == PRO_BN_RELU && inb[u]) {   // zero padding applies to the ACTIVATION: out-of-image stays 0
-                    uint32_t w[4] = {o.x, o.y, o.z, o.w};
+    for (int u = 0; u < ROUNDS; u++) {
+        const int pix = pix0 + 16 * u;
+        if (pix < HPIX) {
+            uint4 o = v[u];
+            if (PRO == PRO_BN_RELU && ((inb >> u) & 1u)) {   // zero padding applies to the ACTIVATION: out-of-image stays 0
+                uint32_t w[4] = {o.x, o.y, o.z, o.w};
 #pragma unroll
-                    for (int j = 0; j < 4; j++) {
-                        const float2 f = unpack_bf16(w[j]);
-                        const float y0 = fmaxf(fmaf(f.x, sc[2 * j], sh[2 * j]), 0.0f);
-                        const float y1 = fmaxf(fmaf(f.y, sc[2 * j + 1], sh[2 * j + 1]), 0.0f);
-                        w[j] = pack_bf16(y0, y1);
-                    }
-                    o = make_uint4(w[0], w[1], w[2], w[3]);
+                for (int j = 0; j < 4; j++) {
+                    const float2 f = unpack_bf16(w[j]);
+                    const float y0 = fmaxf(fmaf(f.x, sc[2 * j], sh[2 * j]), 0.0f);
+                    const float y1 = fmaxf(fmaf(f.y, sc[2 * j + 1], sh[2 * j + 1]), 0.0f);
+                    w[j] = pack_bf16(y0, y1);
                 }
-                *reinterpret_cast<uint4 *>(dst_plane + px[u] * 16) = o;
+                o = make_uint4(w[0], w[1], w[2], w[3]);
             }
+            *reinterpret_cast<uint4 *>(dst_plane + pix * 16) = o;
         }
     }
 }
 
 // ------------------------------------------------------------------ epilogue
-// One warp, one 32-pixel quarter of a tile half: TMEM row -> BF16 -> smem transpose, per-channel
-// statistics from the rounded values, coalesced 512-B stores.
+// One warp, one 32-pixel quarter of a tile half: TMEM row -> BF16 -> smem transpose -> coalesced
+// 512-B stores.  In the transposed phase a lane always holds the same 8 channels (chunk lane%8),
+// so the per-channel sums (batch statistics / BatchNorm-backward sums) are plain per-thread
+// accumulators over everything the thread stores, reduced once at the end of the kernel.
+struct EpiCoef { float sc[8], sh[8], mu[8], is[8]; };
+
 template <int EPI>
 __device__ __forceinline__ void epilogue_half(const ConvArgs &a, uint32_t tmem_addr, uint8_t *stg, int lane, int warp,
-                                              int ty_base, int tx_base, float (&acc0)[2], float (&acc1)[2])
+                                              int ty_base, int tx_base, float (&acc0)[8], float (&acc1)[8],
+                                              const EpiCoef &cf)
 {
+    const int chunk = lane & 7;
+    // the layer below's pre-activation for this lane's 8 pixels: issued first, consumed last
+    uint4 zz[8];
+    uint32_t inbm = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        const int q = (lane >> 3) + 4 * i;
+        const int gy = ty_base + warp * 4 + (q >> 3), gx = tx_base + (q & 7);
+        const bool ok = gy < a.H && gx < a.W;
+        inbm |= (ok ? 1u : 0u) << i;
+        if (EPI == EPI_DGRAD_BN || EPI == EPI_DGRAD_RELU) {
+            zz[i] = make_uint4(0, 0, 0, 0);
+            if (ok) zz[i] = __ldg(reinterpret_cast<const uint4 *>(a.zprev + ((size_t)gy * a.W + gx) * 64 + chunk * 8));
+        }
+    }
     // this thread's accumulator row m = 32*warp + lane  <->  pixel (tile row m/8, column m%8 of the half)
-    uint32_t r[32];
     uint8_t *myrow = stg + lane * EPI_ROW;
 #pragma unroll
     for (int part = 0; part < 2; part++) {
+        uint32_t r[32];
         tmem_ld32(tmem_addr + part * 32, r);
         tmem_ld_wait();
 #pragma unroll
@@ -152,27 +175,28 @@ __device__ __forceinline__ void epilogue_half(const ConvArgs &a, uint32_t tmem_a
     }
     __syncwarp();
     // transposed phase: lane handles chunk (lane % 8) of pixels q = lane/8 + 4*i  (4 pixels = 512 contiguous bytes)
-    const int chunk = lane & 7;
 #pragma unroll
     for (int i = 0; i < 8; i++) {
         const int q = (lane >> 3) + 4 * i;           // pixel index within the warp's 32
         const int gy = ty_base + warp * 4 + (q >> 3), gx = tx_base + (q & 7);
         uint4 o = *reinterpret_cast<const uint4 *>(stg + q * EPI_ROW + chunk * 16);
-        const bool inb = gy < a.H && gx < a.W;
+        const bool inb = (inbm >> i) & 1u;
+        uint32_t w[4] = {o.x, o.y, o.z, o.w};
         if (EPI == EPI_DGRAD_BN || EPI == EPI_DGRAD_RELU) {
             // ReLU mask of the layer below (and its BN-backward sums), net.py:16-18 backward
-            uint32_t w[4] = {o.x, o.y, o.z, o.w};
-            uint4 zz = make_uint4(0, 0, 0, 0);
-            if (inb) zz = __ldg(reinterpret_cast<const uint4 *>(a.zprev + ((size_t)gy * a.W + gx) * 64 + chunk * 8));
-            const uint32_t zw[4] = {zz.x, zz.y, zz.z, zz.w};
+            const uint32_t zw[4] = {zz[i].x, zz[i].y, zz[i].z, zz[i].w};
 #pragma unroll
             for (int j = 0; j < 4; j++) {
                 float2 g = unpack_bf16(w[j]);
                 const float2 z = unpack_bf16(zw[j]);
                 if (EPI == EPI_DGRAD_BN) {
-                    const int c = chunk * 8 + 2 * j;
-                    if (!(fmaf(z.x, a.p_scale[c], a.p_shift[c]) > 0.0f)) g.x = 0.0f;
-                    if (!(fmaf(z.y, a.p_scale[c + 1], a.p_shift[c + 1]) > 0.0f)) g.y = 0.0f;
+                    if (!(fmaf(z.x, cf.sc[2 * j], cf.sh[2 * j]) > 0.0f)) g.x = 0.0f;
+                    if (!(fmaf(z.y, cf.sc[2 * j + 1], cf.sh[2 * j + 1]) > 0.0f)) g.y = 0.0f;
+                    if (inb) {
+                        acc0[2 * j] += g.x; acc0[2 * j + 1] += g.y;
+                        acc1[2 * j] = fmaf(g.x, (z.x - cf.mu[2 * j]) * cf.is[2 * j], acc1[2 * j]);
+                        acc1[2 * j + 1] = fmaf(g.y, (z.y - cf.mu[2 * j + 1]) * cf.is[2 * j + 1], acc1[2 * j + 1]);
+                    }
                 } else {
                     if (!(z.x > 0.0f)) g.x = 0.0f;
                     if (!(z.y > 0.0f)) g.y = 0.0f;
@@ -180,33 +204,16 @@ __device__ __forceinline__ void epilogue_half(const ConvArgs &a, uint32_t tmem_a
                 w[j] = pack_bf16(g.x, g.y);
             }
             o = make_uint4(w[0], w[1], w[2], w[3]);
-            if (EPI == EPI_DGRAD_BN) *reinterpret_cast<uint4 *>(stg + q * EPI_ROW + chunk * 16) = o;   // for the sums below
         }
-        if (inb) *reinterpret_cast<uint4 *>(a.out + ((size_t)gy * a.W + gx) * 64 + chunk * 8) = o;
-    }
-    if (EPI == EPI_STATS || EPI == EPI_DGRAD_BN) {
-        if (EPI == EPI_DGRAD_BN) __syncwarp();
-        // lane owns channels 2*lane, 2*lane+1; sums over the warp's 32 pixels (only those inside the image)
-        float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
-        const int c = 2 * lane;
-        float m0 = 0.f, m1 = 0.f, i0 = 0.f, i1 = 0.f;
-        if (EPI == EPI_DGRAD_BN) { m0 = a.p_mean[c]; m1 = a.p_mean[c + 1]; i0 = a.p_invstd[c]; i1 = a.p_invstd[c + 1]; }
-#pragma unroll 8
-        for (int q = 0; q < 32; q++) {
-            const int gy = ty_base + warp * 4 + (q >> 3), gx = tx_base + (q & 7);
-            if (gy < a.H && gx < a.W) {
-                const float2 v = unpack_bf16(*reinterpret_cast<const uint32_t *>(stg + q * EPI_ROW + lane * 4));
-                if (EPI == EPI_STATS) {
-                    s0 += v.x; s1 += v.y;
-                    q0 = fmaf(v.x, v.x, q0); q1 = fmaf(v.y, v.y, q1);
-                } else {
-                    const float2 z = unpack_bf16(__ldg(reinterpret_cast<const uint32_t *>(a.zprev + ((size_t)gy * a.W + gx) * 64 + c)));
-                    s0 += v.x; s1 += v.y;
-                    q0 = fmaf(v.x, (z.x - m0) * i0, q0); q1 = fmaf(v.y, (z.y - m1) * i1, q1);
-                }
+        if (EPI == EPI_STATS && inb) {
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const float2 v = unpack_bf16(w[j]);
+                acc0[2 * j] += v.x; acc0[2 * j + 1] += v.y;
+                acc1[2 * j] = fmaf(v.x, v.x, acc1[2 * j]); acc1[2 * j + 1] = fmaf(v.y, v.y, acc1[2 * j + 1]);
             }
         }
-        acc0[0] += s0; acc0[1] += s1; acc1[0] += q0; acc1[1] += q1;
+        if (inb) *reinterpret_cast<uint4 *>(a.out + ((size_t)gy * a.W + gx) * 64 + chunk * 8) = o;
     }
     __syncwarp();
 }
@@ -230,23 +237,24 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv64(ConvArgs a)
         mbar_init(BAR(10), 1);
         mbar_fence_init();
     }
-    if (warp == 8) tmem_alloc(smem_u32(tmem_ptr), TMEM_COLS);
+    if (warp == MMA_WARP) tmem_alloc(smem_u32(tmem_ptr), TMEM_COLS);
     fence_before_sync();
     __syncthreads();
     fence_after_sync();
     const uint32_t tmem_base = *tmem_ptr;
 
-    if (warp >= 4 && warp < 8) {
-        // ===== producers =====
-        const int ptid = threadIdx.x - 128;
+    if (warp >= 4 && warp < MMA_WARP) {
+        // ===== producers: group 0 (warps 4-7) stages tiles it = 0, 2, 4, ...; group 1 (warps 8-11) the odd ones =====
+        const int group = (warp - 4) >> 2;
+        const int ptid = (threadIdx.x - 128) & 127;
         float sc[8], sh[8];
 #pragma unroll
         for (int j = 0; j < 8; j++) {
             sc[j] = PRO == PRO_BN_RELU ? a.scale[(ptid & 7) * 8 + j] : 1.0f;
             sh[j] = PRO == PRO_BN_RELU ? a.shift[(ptid & 7) * 8 + j] : 0.0f;
         }
-        int it = 0;
-        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it++) {
+        int it = group;
+        for (int tile = blockIdx.x + group * gridDim.x; tile < ntiles; tile += 2 * gridDim.x, it += 2) {
             const int s = it % STAGES;
             const uint32_t ph = (it / STAGES) & 1;
             mbar_wait(BAR(3 + s), ph ^ 1);                 // slot free (first pass returns immediately)
@@ -254,7 +262,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv64(ConvArgs a)
             fence_proxy_async();                           // st.shared -> visible to the tensor core's async proxy
             mbar_arrive(BAR(s));
         }
-    } else if (warp == 8) {
+    } else if (warp == MMA_WARP) {
         // ===== MMA issuer =====
         if (lane == 0) {
             // weights: one bulk copy by the TMA engine, resident for the whole kernel
@@ -292,8 +300,17 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv64(ConvArgs a)
     } else {
         // ===== epilogue =====
         uint8_t *stg = smem + OFF_EPI + warp * EPI_WARP;
-        float acc0[2] = {0.f, 0.f}, acc1[2] = {0.f, 0.f};
-        double d0[2] = {0.0, 0.0}, d1[2] = {0.0, 0.0};
+        float acc0[8], acc1[8];
+        EpiCoef cf;
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            acc0[j] = acc1[j] = 0.0f;
+            const int c = (lane & 7) * 8 + j;
+            cf.sc[j] = EPI == EPI_DGRAD_BN ? a.p_scale[c] : 1.0f;
+            cf.sh[j] = EPI == EPI_DGRAD_BN ? a.p_shift[c] : 0.0f;
+            cf.mu[j] = EPI == EPI_DGRAD_BN ? a.p_mean[c] : 0.0f;
+            cf.is[j] = EPI == EPI_DGRAD_BN ? a.p_invstd[c] : 1.0f;
+        }
         int it = 0;
         for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it++) {
             const int b = it & 1;
@@ -303,24 +320,31 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv64(ConvArgs a)
 #pragma unroll 1
             for (int h = 0; h < 2; h++)
                 epilogue_half<EPI>(a, tmem_base + ((uint32_t)(warp * 32) << 16) + b * 128 + h * 64, stg, lane, warp, ty,
-                                   tx + h * 8, acc0, acc1);
+                                   tx + h * 8, acc0, acc1, cf);
             fence_before_sync();
             mbar_arrive(BAR(8 + b));
-            if (EPI == EPI_STATS || EPI == EPI_DGRAD_BN) {   // fold the tile's FP32 partials into doubles
-                d0[0] += acc0[0]; d0[1] += acc0[1]; d1[0] += acc1[0]; d1[1] += acc1[1];
-                acc0[0] = acc0[1] = acc1[0] = acc1[1] = 0.f;
-            }
         }
         if ((EPI == EPI_STATS || EPI == EPI_DGRAD_BN) && a.stats) {
-            atomicAdd(a.stats + 2 * lane, d0[0]);
-            atomicAdd(a.stats + 2 * lane + 1, d0[1]);
-            atomicAdd(a.stats + 64 + 2 * lane, d1[0]);
-            atomicAdd(a.stats + 64 + 2 * lane + 1, d1[1]);
+            // lanes l, l+8, l+16, l+24 hold the same 8 channels
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                acc0[j] += __shfl_xor_sync(0xffffffffu, acc0[j], 8);
+                acc0[j] += __shfl_xor_sync(0xffffffffu, acc0[j], 16);
+                acc1[j] += __shfl_xor_sync(0xffffffffu, acc1[j], 8);
+                acc1[j] += __shfl_xor_sync(0xffffffffu, acc1[j], 16);
+            }
+            if (lane < 8) {
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    atomicAdd(a.stats + lane * 8 + j, (double)acc0[j]);
+                    atomicAdd(a.stats + 64 + lane * 8 + j, (double)acc1[j]);
+                }
+            }
         }
     }
     fence_before_sync();
     __syncthreads();
-    if (warp == 8) tmem_dealloc(tmem_base, TMEM_COLS);
+    if (warp == MMA_WARP) tmem_dealloc(tmem_base, TMEM_COLS);
 }
 
 // Weight layout transform: PyTorch conv weight [oc][ic][3][3] fp32 -> the smem image of B for

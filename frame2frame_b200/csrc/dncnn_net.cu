@@ -887,4 +887,21 @@ int f2f_adam_step(float *d_p, const float *d_g, float *d_m, float *d_v, size_t n
     return F2F_OK;
 }
 
+// One inner iteration of blind_denoising.py:216-222 as a single call: train-mode forward
+// (out = curr - net(curr)), masked loss against the pre-warped previous frame, backward, Adam.
+int f2f_step_train(float *d_params, float *d_grads, float *d_m, float *d_v, float *d_bn_running, long long *d_nbt,
+                   const float *d_curr, const float *d_warped, const float *d_mask, float *d_out, float *d_dout,
+                   double *d_loss, void *d_ws, size_t ws_bytes, int H, int W, int loss_kind, long long step, float lr,
+                   float beta1, float beta2, float eps, float weight_decay, void *stream)
+{
+    if (!d_out || !d_dout || !d_loss) { set_error("f2f_step_train: bad arguments"); return F2F_EINVAL; }
+    int rc = f2f_dncnn_forward(d_params, d_bn_running, d_nbt, d_curr, d_out, d_ws, ws_bytes, 1, H, W, 1, 1, stream);
+    if (rc) return rc;
+    rc = f2f_masked_loss(d_out, d_warped, d_mask, d_dout, d_loss, (size_t)H * W, loss_kind, stream);
+    if (rc) return rc;
+    rc = f2f_dncnn_backward(d_params, d_grads, d_dout, d_ws, ws_bytes, 1, H, W, 1, 0, stream);
+    if (rc) return rc;
+    return f2f_adam_step(d_params, d_grads, d_m, d_v, NPARAMS, step, lr, beta1, beta2, eps, weight_decay, stream);
+}
+
 }  // extern "C"

@@ -231,6 +231,38 @@ class Adam(torch.optim.Optimizer):
             ptr += t.numel() * 4
         return True
 
+    def _flat_group_state(self, gi, ps):
+        st = self._flat_state.get(gi)
+        if st is None:
+            n = sum(p.numel() for p in ps)
+            st = self._flat_state[gi] = {
+                "step": 0,
+                "exp_avg": torch.zeros(n, dtype=torch.float32, device=ps[0].device),
+                "exp_avg_sq": torch.zeros(n, dtype=torch.float32, device=ps[0].device)}
+            off = 0
+            for p in ps:
+                k = p.numel()
+                self.state[p] = {"step": torch.tensor(0.0), "exp_avg": st["exp_avg"][off:off + k].view(p.shape),
+                                 "exp_avg_sq": st["exp_avg_sq"][off:off + k].view(p.shape)}
+                off += k
+        return st
+
+    def fused_state(self, model):
+        """For the one-call training step (f2f_step_train): the flat Adam state of `model`'s
+        parameters; the caller passes st["step"] + 1 to the kernel and then calls advance()."""
+        group = self.param_groups[0]
+        ps = list(group["params"])
+        if len(self.param_groups) != 1 or not self._contiguous_run([p.data for p in ps]) \
+                or ps[0].data_ptr() != model.flat_params.data_ptr():
+            raise RuntimeError("fused step needs an optimizer built from model.parameters() of one DnCNN")
+        return self._flat_group_state(0, ps), group
+
+    def advance(self):
+        st = self._flat_state[0]
+        st["step"] += 1
+        for p in self.param_groups[0]["params"]:
+            self.state[p]["step"] += 1
+
     @torch.no_grad()
     def step(self, closure=None):
         loss = None
@@ -246,18 +278,7 @@ class Adam(torch.optim.Optimizer):
                 and self._contiguous_run([p.grad for p in ps])
             if flat:
                 n = sum(p.numel() for p in ps)
-                st = self._flat_state.get(gi)
-                if st is None:
-                    st = self._flat_state[gi] = {
-                        "step": 0,
-                        "exp_avg": torch.zeros(n, dtype=torch.float32, device=ps[0].device),
-                        "exp_avg_sq": torch.zeros(n, dtype=torch.float32, device=ps[0].device)}
-                    off = 0
-                    for p in ps:
-                        k = p.numel()
-                        self.state[p] = {"step": torch.tensor(0.0), "exp_avg": st["exp_avg"][off:off + k].view(p.shape),
-                                         "exp_avg_sq": st["exp_avg_sq"][off:off + k].view(p.shape)}
-                        off += k
+                st = self._flat_group_state(gi, ps)
                 st["step"] += 1
                 for p in ps:
                     self.state[p]["step"] += 1

@@ -90,3 +90,14 @@ def dncnn_state_dict(seed=0, channels=1, num_of_layers=17, features=64, prefix="
         idx += 3
     conv(idx, channels, features)
     return sd
+
+
+def pretrained_state_dict(path=None):
+    """The DnCNN-S-25-layout denoiser trained on synthetic textures by tools/pretrain_dncnn.py
+    (stand-in for the un-vendored dncnn/logs/DnCNN-S-25/net.pth), `module.`-prefixed,
+    as float32 numpy arrays."""
+    import os
+    if path is None:
+        path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden",
+                            "dncnn_s25_synth.npz")
+    return {k: (np.asarray(v, np.float32) if v.dtype.kind == "f" else np.asarray(v)) for k, v in np.load(path).items()}

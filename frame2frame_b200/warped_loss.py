@@ -77,7 +77,10 @@ class WarpedLoss(nn.Module):
         self._cache = None
 
     def cuda(self, device=None):
-        self._dev = torch.device("cuda", torch.cuda.current_device() if device is None else device)
+        if isinstance(device, torch.device):
+            self._dev = device if device.index is not None else torch.device("cuda", torch.cuda.current_device())
+        else:
+            self._dev = torch.device("cuda", torch.cuda.current_device() if device is None else device)
         return self
 
     def _device(self, *ts):

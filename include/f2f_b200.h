@@ -226,6 +226,17 @@ int f2f_adam_step(float *d_p, const float *d_g, float *d_m, float *d_v, size_t n
                   long long step, float lr, float beta1, float beta2, float eps,
                   float weight_decay, void *stream);
 
+/* One inner iteration of the reference's fine-tuning loop (blind_denoising.py:216-222) in one
+ * call: out = curr - net(curr) in train mode, loss = masked loss of out against the pre-warped
+ * previous frame (f2f_warp_mask output; kinds as f2f_masked_loss), backward, Adam step `step`.
+ * d_out, d_dout: [H][W] scratch (d_out holds the train-mode output afterwards); *d_loss: device
+ * double. */
+int f2f_step_train(float *d_params, float *d_grads, float *d_m, float *d_v, float *d_bn_running,
+                   long long *d_nbt, const float *d_curr, const float *d_warped,
+                   const float *d_mask, float *d_out, float *d_dout, double *d_loss, void *d_ws,
+                   size_t ws_bytes, int H, int W, int loss_kind, long long step, float lr,
+                   float beta1, float beta2, float eps, float weight_decay, void *stream);
+
 /* Measurement hooks for bench.py.  While enabled, the TV-L1 batch brackets the
  * finest-scale inner-iteration launches with CUDA events on the caller's
  * stream (and synchronises at the end of each group to read them).
