@@ -37,55 +37,7 @@ PAIRS_PER_STEP = 16          # per GPU; 16 pairs x 2 frames x 8.3 MB = 265 MB > 
 ALG_BYTES_PER_PX_ITER = 64   # read rho_c,I1wx,I1wy,grad,u1,u2,p11..p22; write u1,u2,p11..p22
 
 
-def peaks():
-    try:
-        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))), "measured"
-    except Exception:
-        return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
-
-
-class ClockSampler:
-    """nvidia-smi clocks / throttle reasons during the timed region."""
-    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
-
-    def __init__(self, index):
-        self.samples, self.proc = [], None
-        try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "200"],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.t = threading.Thread(target=self._read, daemon=True)
-            self.t.start()
-        except Exception:
-            self.proc = None
-
-    def _read(self):
-        for line in self.proc.stdout:
-            self.samples.append(line.strip())
-
-    def stop(self):
-        if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.25)
-        self.proc.terminate()
-        sm, mx, reasons = [], None, set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for s in self.samples:
-            f = [x.strip() for x in s.split(",")]
-            if len(f) < 6:
-                continue
-            try:
-                sm.append(float(f[0]))
-                mx = float(f[1])
-            except ValueError:
-                continue
-            for n, v in zip(names, f[2:6]):
-                if v.lower().startswith("active"):
-                    reasons.add(n)
-        sm.sort()
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
-                "samples": len(sm)}
+from frame2frame_b200.benchutil import ClockSampler, peaks  # noqa: E402
 
 
 def make_pairs(n, seq):
@@ -160,7 +112,7 @@ def cpu_baseline(seconds_budget=25.0):
             "sample": "%d pair(s) 1920x1080 in %.1f s, OpenMP %d threads" % (n, dt, cores)}
 
 
-def ours_tvl1(args, rank, world, local_rank):
+def ours_tvl1(args, rank, world, local_rank, with_cpu=True):
     import numpy as np
     import torch
     import torch.distributed as dist
@@ -259,9 +211,9 @@ def ours_tvl1(args, rank, world, local_rank):
                      "traffic": 2.148e9, "traffic_note": "dram read+write per launch of 16 slots, ncu --set full, "
                                                          "profiles/r01_tvl1_iter_strip.md"},
     }
-    if world == 1 and not args.no_cpu:
+    if world == 1 and not args.no_cpu and with_cpu:
         line["cpu_baseline"] = cpu_baseline()
-    print(json.dumps(line))
+    return line
 
 
 def main():
@@ -270,14 +222,19 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="tvl1", choices=["tvl1"])
+    ap.add_argument("--workload", default="f2f", choices=["f2f", "tvl1"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-tvl1", action="store_true", help="f2f workload: skip the secondary TV-L1 measurement")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    import bench_f2f
     if args.impl == "reference":
-        reference_arm(args, rank, world)
+        if args.workload == "f2f":
+            bench_f2f.reference_arm(args, rank, world)
+        else:
+            reference_arm(args, rank, world)
         return
     import torch
     if not torch.cuda.is_available():
@@ -287,7 +244,20 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     try:
-        ours_tvl1(args, rank, world, local_rank)
+        if args.workload == "tvl1":
+            line = ours_tvl1(args, rank, world, local_rank)
+        else:
+            line = bench_f2f.ours(args, rank, world, local_rank, ClockSampler, peaks)
+            if not args.no_tvl1:
+                # the metric's second half (TV-L1 flow fields/sec, configs[1]) as a short secondary measurement
+                targs = argparse.Namespace(**vars(args))
+                targs.steps, targs.warmup = 2, 3
+                t = ours_tvl1(targs, rank, world, local_rank, with_cpu=True)
+                if rank == 0:
+                    line["tvl1"] = {k: t[k] for k in ("metric", "value", "unit", "ms_per_step", "config", "e2e", "roofline",
+                                                      "cpu_baseline") if k in t}
+        if rank == 0:
+            print(json.dumps(line))
     finally:
         if world > 1:
             import torch.distributed as dist

@@ -57,6 +57,10 @@ def _declare(lib):
                                   C.c_float, vp]
     lib.f2f_step_train.argtypes = [fp, fp, fp, fp, fp, vp, fp, fp, fp, fp, fp, vp, vp, sz, C.c_int, C.c_int, C.c_int,
                                    C.c_longlong, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, vp]
+    lib.f2f_profile_dncnn.argtypes = [C.c_int]
+    lib.f2f_profile_dncnn.restype = None
+    lib.f2f_profile_dncnn_read.argtypes = [C.POINTER(C.c_double)]
+    lib.f2f_profile_dncnn_read.restype = None
     lib.f2f_profile_enable.argtypes = [C.c_int]
     lib.f2f_profile_enable.restype = None
     lib.f2f_profile_read.argtypes = [C.POINTER(C.c_double)]

@@ -28,12 +28,44 @@
 //               warps take alternate tiles, each with the whole haloed tile's loads in flight at
 //               once (the layer is within ~20% of being HBM-bound, so bytes in flight matter)
 //   warp  12    MMA issuer (72 tcgen05.mma per tile into a double-buffered accumulator) + TMEM owner
+#include <vector>
 #include "f2f_common.cuh"
 #include "tc05.cuh"
 
 namespace f2f {
 
 long g_dncnn_launches = 0;
+
+// ---- per-launch CUDA-event timing of the tensor-core kernels (f2f_profile_dncnn) ----
+namespace {
+struct ProfClass {
+    std::vector<cudaEvent_t> ev;   // pairs: begin, end
+    size_t used = 0;
+};
+ProfClass g_prof_cls[2];
+bool g_prof_on = false;
+}  // namespace
+
+void prof_begin(int cls, cudaStream_t st)
+{
+    if (!g_prof_on) return;
+    ProfClass &p = g_prof_cls[cls];
+    if (p.used + 2 > p.ev.size()) {
+        for (int i = 0; i < 2; i++) {
+            cudaEvent_t e;
+            cudaEventCreate(&e);
+            p.ev.push_back(e);
+        }
+    }
+    cudaEventRecord(p.ev[p.used], st);
+}
+void prof_end(int cls, cudaStream_t st)
+{
+    if (!g_prof_on) return;
+    ProfClass &p = g_prof_cls[cls];
+    cudaEventRecord(p.ev[p.used + 1], st);
+    p.used += 2;
+}
 
 namespace dn {
 
@@ -376,7 +408,9 @@ static int launch_conv64(const ConvArgs &a, cudaStream_t st)
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const int ntiles = a.tiles_x * a.tiles_y;
     const int grid = ntiles < sms ? ntiles : sms;
+    prof_begin(0, st);
     k_conv64<PRO, EPI><<<grid, NTHREADS, SMEM_BYTES, st>>>(a);
+    prof_end(0, st);
     g_dncnn_launches++;
     F2F_LAUNCH_CHECK();
     return F2F_OK;
@@ -389,6 +423,27 @@ using namespace f2f;
 using namespace f2f::dn;
 
 extern "C" {
+
+void f2f_profile_dncnn(int on)
+{
+    for (auto &p : g_prof_cls) p.used = 0;
+    g_prof_on = on != 0;
+}
+
+void f2f_profile_dncnn_read(double out[4])
+{
+    for (int c = 0; c < 2; c++) {
+        ProfClass &p = g_prof_cls[c];
+        double ms = 0.0;
+        for (size_t i = 0; i + 1 < p.used; i += 2) {
+            cudaEventSynchronize(p.ev[i + 1]);
+            float t = 0.f;
+            if (cudaEventElapsedTime(&t, p.ev[i], p.ev[i + 1]) == cudaSuccess) ms += t;
+        }
+        out[2 * c] = ms;
+        out[2 * c + 1] = (double)(p.used / 2);
+    }
+}
 
 int f2f_dncnn_prep_w64(const float *d_w, void *d_wprep, int transpose, void *stream)
 {

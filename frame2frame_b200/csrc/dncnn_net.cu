@@ -777,7 +777,9 @@ int f2f_dncnn_wgrad64(const void *d_act, const float *d_coef_in, void *d_g, cons
     a.partial = d_partial; a.H = H; a.W = W; a.tiles_x = cdiv(W, 16); a.tiles_y = cdiv(H, 16);
     const int ntiles = a.tiles_x * a.tiles_y;
     const int grid = ntiles < num_sms() ? ntiles : num_sms();
+    prof_begin(1, st);
     wg::k_wgrad64<<<grid, wg::NTHREADS, wg::SMEM_BYTES, st>>>(a);
+    prof_end(1, st);
     wg::k_wgrad_reduce<<<cdiv(9 * 4096, 256), 256, 0, st>>>(d_partial, grid, d_dw, accumulate);
     g_dncnn_launches += 2;
     F2F_LAUNCH_CHECK();

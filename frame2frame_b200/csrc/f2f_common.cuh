@@ -21,6 +21,11 @@ void set_error(const char *fmt, ...);
 
 #define F2F_LAUNCH_CHECK() F2F_CUDA_CHECK(cudaGetLastError())
 
+// bench.py's measurement hook for the DnCNN kernels (dncnn.cu): while enabled, launches of class
+// 0 (64->64 conv / dgrad) and 1 (64->64 wgrad) are bracketed with CUDA events on their stream.
+void prof_begin(int cls, cudaStream_t st);
+void prof_end(int cls, cudaStream_t st);
+
 static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 

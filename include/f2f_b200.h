@@ -247,6 +247,13 @@ int f2f_step_train(float *d_params, float *d_grads, float *d_m, float *d_v, floa
 void f2f_profile_enable(int on);
 void f2f_profile_read(double out[5]);
 
+/* Same for the DnCNN tensor-core kernels: while on, every 64->64 convolution / input-gradient
+ * launch (class 0) and weight-gradient launch (class 1) is bracketed with CUDA events on its
+ * stream.  f2f_profile_dncnn(1) also resets the counters.  f2f_profile_dncnn_read synchronises
+ * those events: out[0] = ms in class-0 launches, out[1] = their number, out[2], out[3] = class 1. */
+void f2f_profile_dncnn(int on);
+void f2f_profile_dncnn_read(double out[4]);
+
 /* Compares the iteration kernel's in-line correctly-rounded division with IEEE
  * division on n pseudo-random operand pairs in the ranges the solver produces;
  * *h_mismatches receives the number of differing results (expected 0). */
