@@ -28,6 +28,7 @@
 //               warps take alternate tiles, each with the whole haloed tile's loads in flight at
 //               once (the layer is within ~20% of being HBM-bound, so bytes in flight matter)
 //   warp  12    MMA issuer (72 tcgen05.mma per tile into a double-buffered accumulator) + TMEM owner
+#include <cuda.h>
 #include <vector>
 #include "f2f_common.cuh"
 #include "tc05.cuh"
@@ -108,7 +109,10 @@ struct ConvArgs {
     const float *p_mean;
     const float *p_invstd;
     int H, W, tiles_x, tiles_y;
+    unsigned long long *trace;   // f2f_dncnn_set_trace: per-role cycle counters (development aid) or NULL
 };
+
+unsigned long long *g_conv_trace = nullptr;
 
 // ------------------------------------------------------------------ producer
 // Stages one haloed tile: 324 pixels x 8 chunks of 16 B.  Thread t of the 128-thread group owns
@@ -255,7 +259,9 @@ template <int PRO, int EPI>
 __global__ void __launch_bounds__(NTHREADS, 1) k_conv64(ConvArgs a)
 {
     extern __shared__ __align__(1024) uint8_t smem[];
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // the shuffle makes the warp index provably warp-uniform for ptxas: role branches are then uniform
+    // branches and the MMA warp's descriptor arithmetic can live in uniform registers
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
     const int ntiles = a.tiles_x * a.tiles_y;
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + OFF_BAR);
     // barrier slots: full[3] @0, empty[3] @3, tfull[2] @6, tempty[2] @8, wbar @10; tmem base pointer @ +12
@@ -286,47 +292,72 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv64(ConvArgs a)
             sh[j] = PRO == PRO_BN_RELU ? a.shift[(ptid & 7) * 8 + j] : 0.0f;
         }
         int it = group;
+        long long tr_wait = 0, tr_work = 0;
+        const bool tr = a.trace != nullptr && ptid == 0 && group == 0;
         for (int tile = blockIdx.x + group * gridDim.x; tile < ntiles; tile += 2 * gridDim.x, it += 2) {
             const int s = it % STAGES;
             const uint32_t ph = (it / STAGES) & 1;
+            const long long t0 = tr ? clock64() : 0;
             mbar_wait(BAR(3 + s), ph ^ 1);                 // slot free (first pass returns immediately)
+            const long long t1 = tr ? clock64() : 0;
             produce_tile<PRO>(a, tile, smem + OFF_A + s * A_STAGE, ptid, sc, sh);
             fence_proxy_async();                           // st.shared -> visible to the tensor core's async proxy
             mbar_arrive(BAR(s));
+            if (tr) { tr_wait += t1 - t0; tr_work += clock64() - t1; }
         }
+        if (tr) { atomicAdd(a.trace + 0, (unsigned long long)tr_wait); atomicAdd(a.trace + 1, (unsigned long long)tr_work); }
     } else if (warp == MMA_WARP) {
-        // ===== MMA issuer =====
-        if (lane == 0) {
+        // ===== MMA issuer: the warp stays converged, the elected lane issues =====
+        const uint32_t el = elect_one();
+        if (el) {
             // weights: one bulk copy by the TMA engine, resident for the whole kernel
             mbar_arrive_expect_tx(BAR(10), B_BYTES);
             for (int t = 0; t < 9; t++) bulk_g2s(smem_u32(smem + OFF_B + t * B_TAP), a.wprep + (size_t)t * 4096, B_TAP, BAR(10));
-            mbar_wait(BAR(10), 0);
-            constexpr uint32_t IDESC = idesc_bf16(128, 64, 0, 0);
-            int it = 0;
-            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it++) {
-                const int s = it % STAGES, b = it & 1;
-                mbar_wait(BAR(8 + b), ((it >> 1) & 1) ^ 1);   // accumulator buffer drained by the epilogue
-                mbar_wait(BAR(s), (it / STAGES) & 1);          // operand tile staged
-                fence_after_sync();
-                const uint32_t a_base = smem_u32(smem + OFF_A + s * A_STAGE);
-                const uint32_t b_base = smem_u32(smem + OFF_B);
-#pragma unroll 1
-                for (int tap = 0; tap < 9; tap++) {
-                    const int dy = tap / 3, dx = tap % 3;      // halo coordinates of the tap: (dy, dx) in 0..2
-                    const uint32_t a_tap = a_base + (uint32_t)(dy * HW + dx) * 16u;
+        }
+        __syncwarp();
+        mbar_wait(BAR(10), 0);
+        constexpr uint32_t IDESC = idesc_bf16(128, 64, 0, 0);
+        // descriptors differ only in the start-address field (low word, 16-byte units)
+        const uint64_t bd0 = smem_desc(smem_u32(smem + OFF_B), 1024, 128);
+        const uint32_t b_lo = (uint32_t)bd0, b_hi = (uint32_t)(bd0 >> 32);
+        const uint32_t a_hi = (uint32_t)(smem_desc(0, CH_STRIDE, HW * 16) >> 32);
+        const uint32_t a_lo_lbo = (uint32_t)smem_desc(0, CH_STRIDE, HW * 16);
+        const bool tr = a.trace != nullptr && el;
+        long long tr_te = 0, tr_full = 0, tr_issue = 0;
+        int it = 0;
+        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it++) {
+            const int s = it % STAGES, b = it & 1;
+            const long long t0 = tr ? clock64() : 0;
+            mbar_wait(BAR(8 + b), ((it >> 1) & 1) ^ 1);   // accumulator buffer drained by the epilogue
+            const long long t1 = tr ? clock64() : 0;
+            mbar_wait(BAR(s), (it / STAGES) & 1);          // operand tile staged
+            const long long t2 = tr ? clock64() : 0;
+            fence_after_sync();
+            const uint32_t a_lo = a_lo_lbo | ((smem_u32(smem + OFF_A + s * A_STAGE) & 0x3FFFFu) >> 4);
+            const uint32_t d0 = tmem_base + b * 128;
 #pragma unroll
-                    for (int j = 0; j < 4; j++) {              // K = 64 input channels = 4 x 16
-                        const uint64_t bd = smem_desc(b_base + tap * B_TAP + j * 2 * 1024, 1024, 128);
+            for (int tap = 0; tap < 9; tap++) {
+                const int dy = tap / 3, dx = tap % 3;      // halo coordinates of the tap: (dy, dx) in 0..2
 #pragma unroll
-                        for (int h = 0; h < 2; h++) {          // left / right 8 columns of the 16-wide tile
-                            const uint64_t ad = smem_desc(a_tap + h * 8 * 16 + j * 2 * CH_STRIDE, CH_STRIDE, HW * 16);
-                            mma_ss(tmem_base + b * 128 + h * 64, ad, bd, IDESC, (tap | j) != 0);
-                        }
+                for (int j = 0; j < 4; j++) {              // K = 64 input channels = 4 x 16
+                    const uint64_t bd = ((uint64_t)b_hi << 32) | (b_lo + (tap * B_TAP + j * 2 * 1024) / 16);
+#pragma unroll
+                    for (int h = 0; h < 2; h++) {          // left / right 8 columns of the 16-wide tile
+                        const uint64_t ad = ((uint64_t)a_hi << 32) | (a_lo + (dy * HW + dx) + h * 8 + j * (2 * CH_STRIDE / 16));
+                        mma_ss_el(d0 + h * 64, ad, bd, IDESC, (tap | j) != 0, el);
                     }
                 }
+            }
+            if (el) {
                 mma_commit(BAR(3 + s));    // operand slot reusable once these MMAs have read it
                 mma_commit(BAR(6 + b));    // accumulators complete -> epilogue
             }
+            __syncwarp();
+            if (tr) { tr_te += t1 - t0; tr_full += t2 - t1; tr_issue += clock64() - t2; }
+        }
+        if (tr) {
+            atomicAdd(a.trace + 2, (unsigned long long)tr_te); atomicAdd(a.trace + 3, (unsigned long long)tr_full);
+            atomicAdd(a.trace + 4, (unsigned long long)tr_issue); atomicAdd(a.trace + 8, (unsigned long long)it);
         }
         __syncwarp();
     } else {
@@ -344,10 +375,15 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv64(ConvArgs a)
             cf.is[j] = EPI == EPI_DGRAD_BN ? a.p_invstd[c] : 1.0f;
         }
         int it = 0;
+        const bool tr = a.trace != nullptr && threadIdx.x == 0;
+        long long tr_wait = 0, tr_work = 0;
+        const long long tr_start = tr ? clock64() : 0;
         for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it++) {
             const int b = it & 1;
             const int ty = (tile / a.tiles_x) * TH, tx = (tile % a.tiles_x) * TW;
+            const long long t0 = tr ? clock64() : 0;
             mbar_wait(BAR(6 + b), (it >> 1) & 1);
+            const long long t1 = tr ? clock64() : 0;
             fence_after_sync();
 #pragma unroll 1
             for (int h = 0; h < 2; h++)
@@ -355,6 +391,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv64(ConvArgs a)
                                    tx + h * 8, acc0, acc1, cf);
             fence_before_sync();
             mbar_arrive(BAR(8 + b));
+            if (tr) { tr_wait += t1 - t0; tr_work += clock64() - t1; }
+        }
+        if (tr) {
+            atomicAdd(a.trace + 5, (unsigned long long)tr_wait); atomicAdd(a.trace + 6, (unsigned long long)tr_work);
+            atomicAdd(a.trace + 7, (unsigned long long)(clock64() - tr_start));
         }
         if ((EPI == EPI_STATS || EPI == EPI_DGRAD_BN) && a.stats) {
             // lanes l, l+8, l+16, l+24 hold the same 8 channels
@@ -378,6 +419,354 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv64(ConvArgs a)
     __syncthreads();
     if (warp == MMA_WARP) tmem_dealloc(tmem_base, TMEM_COLS);
 }
+
+
+}  // namespace dn
+
+// =====================================================================================
+// dnt -- the TMA-fed variant of the 64->64 convolution, used whenever the operand needs no
+// transform on load (every input-gradient convolution, and the first 64->64 layer).
+//
+// What the per-role cycle trace (f2f_dncnn_set_trace) and tools/ubench_mma.cu showed about the
+// kernel above on B200: (1) an M128 N64 K16 MMA is bound by the shared-memory read of its
+// operands (6 KB per instruction at 128 B/clk = 48 cycles, floor 32), and the SAME array serves
+// every st.shared / ld.shared / global-load fill of the CTA, so bytes through shared memory per
+// pixel, not tensor throughput, set the time; (2) the epilogue, not the MMA, was the critical
+// path of the input-gradient launches: four warps waiting on the global loads of the layer
+// below's pre-activation after every accumulator hand-over.
+//
+// Hence: tile = 16 rows x 8 pixels = ONE M128 block (accumulator = 64 TMEM columns,
+// double-buffered); the haloed 18x10 operand tile is written by one TMA tensor load in the
+// 128-byte-swizzled pixel-major layout (no register round trip, no st.shared, zero fill at the
+// image border for free), taps are shifted views of it; the pre-activation tile the epilogue
+// needs arrives the same way, two tiles ahead; eight epilogue warps drain two tiles at once.
+//
+//   warps 0-3 / 4-7  epilogue of even / odd tiles (TMEM lane quarter = warp % 4)
+//   warp 8           MMA issuer (36 tcgen05.mma per tile) + TMEM owner
+//   warp 9 / 10      TMA producer of the operand tiles / of the pre-activation tiles
+namespace dnt {
+
+using namespace tc05;
+using dn::ConvArgs;
+using dn::EpiCoef;
+using dn::EPI_STORE;
+using dn::EPI_STATS;
+using dn::EPI_DGRAD_BN;
+using dn::EPI_DGRAD_RELU;
+typedef __nv_bfloat16 bf16;
+
+constexpr int TW = 8, TH = 16;
+constexpr int HW = TW + 2, HH = TH + 2, HPIX = HW * HH;   // 10 x 18 = 180 pixels
+constexpr int A_TX = HPIX * 128;                           // bytes one operand load delivers
+constexpr int A_STAGE = 23 * 1024;                         // 23040 rounded up to the swizzle period
+constexpr int NA = 3;
+constexpr int Z_STAGE = TW * TH * 128;                     // 16384
+constexpr int NZ = 3;
+constexpr int B_TAP = 64 * 64 * 2, B_BYTES = 9 * B_TAP;
+constexpr int EPI_ROW = 144, EPI_WARP = 32 * EPI_ROW, NEPI = 8;
+constexpr int OFF_B = 0;
+constexpr int OFF_A = OFF_B + B_BYTES;
+constexpr int OFF_Z = OFF_A + NA * A_STAGE;
+constexpr int OFF_EPI = OFF_Z + NZ * Z_STAGE;
+constexpr int OFF_BAR = OFF_EPI + NEPI * EPI_WARP;
+constexpr int SMEM_BYTES = OFF_BAR + 256 + 1024;           // + slack to align the base to 1024 B
+constexpr int NTHREADS = 11 * 32;
+constexpr int MMA_WARP = 8, TMA_A_WARP = 9, TMA_Z_WARP = 10;
+constexpr int TMEM_COLS = 128;
+// barrier slots
+constexpr int B_FULL_A = 0, B_EMPTY_A = 3, B_FULL_Z = 6, B_EMPTY_Z = 9, B_TFULL = 12, B_TEMPTY = 14, B_W = 16;
+static_assert(SMEM_BYTES <= 232448, "shared memory budget");
+static_assert(OFF_A % 1024 == 0 && OFF_Z % 1024 == 0 && A_STAGE % 1024 == 0, "swizzle alignment");
+
+// One warp, its 32 pixels (4 rows x 8) of a tile: TMEM row -> BF16 -> smem transpose -> in the
+// transposed phase a lane owns chunk lane%8 (8 channels) of pixels q = lane/8 + 4i, so per-channel
+// sums are per-thread accumulators, and reads the layer below's pre-activation from the TMA-fed
+// tile `zst` (128-byte rows, chunk c of pixel p at chunk c ^ (p & 7)).
+template <int EPI>
+__device__ __forceinline__ void epilogue_tile(const ConvArgs &a, uint32_t tmem_addr, uint8_t *stg, const uint8_t *zst,
+                                              uint32_t zbar, uint32_t zphase, int lane, int wq, int ty, int tx,
+                                              float (&acc0)[8], float (&acc1)[8], const EpiCoef &cf)
+{
+    const int chunk = lane & 7;
+    uint8_t *myrow = stg + lane * EPI_ROW;
+#pragma unroll
+    for (int part = 0; part < 2; part++) {
+        uint32_t r[32];
+        tmem_ld32(tmem_addr + part * 32, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            uint4 o;
+            o.x = pack_bf16(__uint_as_float(r[8 * j + 0]), __uint_as_float(r[8 * j + 1]));
+            o.y = pack_bf16(__uint_as_float(r[8 * j + 2]), __uint_as_float(r[8 * j + 3]));
+            o.z = pack_bf16(__uint_as_float(r[8 * j + 4]), __uint_as_float(r[8 * j + 5]));
+            o.w = pack_bf16(__uint_as_float(r[8 * j + 6]), __uint_as_float(r[8 * j + 7]));
+            *reinterpret_cast<uint4 *>(myrow + part * 64 + j * 16) = o;
+        }
+    }
+    __syncwarp();
+    if (EPI == EPI_DGRAD_BN || EPI == EPI_DGRAD_RELU) mbar_wait(zbar, zphase);
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        const int q = (lane >> 3) + 4 * i;           // pixel within the warp's 32
+        const int gy = ty + wq * 4 + (q >> 3), gx = tx + (q & 7);
+        const bool inb = gy < a.H && gx < a.W;
+        uint4 o = *reinterpret_cast<const uint4 *>(stg + q * EPI_ROW + chunk * 16);
+        uint32_t w[4] = {o.x, o.y, o.z, o.w};
+        if (EPI == EPI_DGRAD_BN || EPI == EPI_DGRAD_RELU) {
+            // ReLU mask of the layer below (and its BatchNorm-backward sums), net.py:16-18 backward
+            const int zp = wq * 32 + q;              // pixel within the tile
+            const uint4 zv = *reinterpret_cast<const uint4 *>(zst + zp * 128 + ((chunk ^ (zp & 7)) << 4));
+            const uint32_t zw[4] = {zv.x, zv.y, zv.z, zv.w};
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                float2 g = unpack_bf16(w[j]);
+                const float2 z = unpack_bf16(zw[j]);
+                if (EPI == EPI_DGRAD_BN) {
+                    if (!(fmaf(z.x, cf.sc[2 * j], cf.sh[2 * j]) > 0.0f)) g.x = 0.0f;
+                    if (!(fmaf(z.y, cf.sc[2 * j + 1], cf.sh[2 * j + 1]) > 0.0f)) g.y = 0.0f;
+                    if (inb) {
+                        acc0[2 * j] += g.x; acc0[2 * j + 1] += g.y;
+                        acc1[2 * j] = fmaf(g.x, (z.x - cf.mu[2 * j]) * cf.is[2 * j], acc1[2 * j]);
+                        acc1[2 * j + 1] = fmaf(g.y, (z.y - cf.mu[2 * j + 1]) * cf.is[2 * j + 1], acc1[2 * j + 1]);
+                    }
+                } else {
+                    if (!(z.x > 0.0f)) g.x = 0.0f;
+                    if (!(z.y > 0.0f)) g.y = 0.0f;
+                }
+                w[j] = pack_bf16(g.x, g.y);
+            }
+            o = make_uint4(w[0], w[1], w[2], w[3]);
+        }
+        if (EPI == EPI_STATS && inb) {
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const float2 v = unpack_bf16(w[j]);
+                acc0[2 * j] += v.x; acc0[2 * j + 1] += v.y;
+                acc1[2 * j] = fmaf(v.x, v.x, acc1[2 * j]); acc1[2 * j + 1] = fmaf(v.y, v.y, acc1[2 * j + 1]);
+            }
+        }
+        if (inb) *reinterpret_cast<uint4 *>(a.out + ((size_t)gy * a.W + gx) * 64 + chunk * 8) = o;
+    }
+    __syncwarp();
+}
+
+template <int EPI>
+__global__ void __launch_bounds__(NTHREADS, 1) k_conv64t(ConvArgs a, const __grid_constant__ CUtensorMap tm_in,
+                                                         const __grid_constant__ CUtensorMap tm_z)
+{
+    extern __shared__ uint8_t smem_raw[];
+    // 1024-byte aligned base: the swizzle phase of a TMA-written row is then (row & 7)
+    uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
+    const int ntiles = a.tiles_x * a.tiles_y;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + OFF_BAR);
+    const uint32_t bar0 = smem_u32(bars);
+    auto BAR = [&](int i) { return bar0 + 8u * i; };
+    uint32_t *tmem_ptr = reinterpret_cast<uint32_t *>(bars + 20);
+    constexpr bool DGRAD = EPI == EPI_DGRAD_BN || EPI == EPI_DGRAD_RELU;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < NA; s++) { mbar_init(BAR(B_FULL_A + s), 1); mbar_init(BAR(B_EMPTY_A + s), 1); }
+        for (int s = 0; s < NZ; s++) { mbar_init(BAR(B_FULL_Z + s), 1); mbar_init(BAR(B_EMPTY_Z + s), 4); }
+        for (int b = 0; b < 2; b++) { mbar_init(BAR(B_TFULL + b), 1); mbar_init(BAR(B_TEMPTY + b), 128); }
+        mbar_init(BAR(B_W), 1);
+        mbar_fence_init();
+    }
+    if (warp == MMA_WARP) tmem_alloc(smem_u32(tmem_ptr), TMEM_COLS);
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem_base = *tmem_ptr;
+
+    if (warp == TMA_A_WARP) {
+        // ===== operand tiles: one tensor load per tile (18 rows x 10 pixels x 128 B, zero fill outside) =====
+        if (elect_one()) {
+            tma_prefetch_desc(&tm_in);
+            const bool tr = a.trace != nullptr;
+            long long tr_wait = 0;
+            int it = 0;
+            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it++) {
+                const int s = it % NA;
+                const int ty0 = (tile / a.tiles_x) * TH - 1, tx0 = (tile % a.tiles_x) * TW - 1;
+                const long long t0 = tr ? clock64() : 0;
+                mbar_wait(BAR(B_EMPTY_A + s), ((it / NA) & 1) ^ 1);
+                if (tr) tr_wait += clock64() - t0;
+                mbar_arrive_expect_tx(BAR(B_FULL_A + s), A_TX);
+                tma_load_3d(smem_u32(smem + OFF_A + s * A_STAGE), &tm_in, BAR(B_FULL_A + s), 0, tx0, ty0);
+            }
+            if (tr) atomicAdd(a.trace + 0, (unsigned long long)tr_wait);
+        }
+        __syncwarp();
+    } else if (warp == TMA_Z_WARP) {
+        // ===== the layer below's pre-activation for the epilogue (16 rows x 8 pixels x 128 B) =====
+        if (DGRAD && elect_one()) {
+            tma_prefetch_desc(&tm_z);
+            int it = 0;
+            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it++) {
+                const int s = it % NZ;
+                const int ty0 = (tile / a.tiles_x) * TH, tx0 = (tile % a.tiles_x) * TW;
+                mbar_wait(BAR(B_EMPTY_Z + s), ((it / NZ) & 1) ^ 1);
+                mbar_arrive_expect_tx(BAR(B_FULL_Z + s), Z_STAGE);
+                tma_load_3d(smem_u32(smem + OFF_Z + s * Z_STAGE), &tm_z, BAR(B_FULL_Z + s), 0, tx0, ty0);
+            }
+        }
+        __syncwarp();
+    } else if (warp == MMA_WARP) {
+        // ===== MMA issuer: the warp stays converged, the elected lane issues =====
+        const uint32_t el = elect_one();
+        if (el) {
+            mbar_arrive_expect_tx(BAR(B_W), B_BYTES);
+            for (int t = 0; t < 9; t++) bulk_g2s(smem_u32(smem + OFF_B + t * B_TAP), a.wprep + (size_t)t * 4096, B_TAP, BAR(B_W));
+        }
+        __syncwarp();
+        mbar_wait(BAR(B_W), 0);
+        constexpr uint32_t IDESC = idesc_bf16(128, 64, 0, 0);
+        const uint64_t bd0 = smem_desc(smem_u32(smem + OFF_B), 1024, 128);
+        const uint32_t b_lo = (uint32_t)bd0, b_hi = (uint32_t)(bd0 >> 32);
+        const uint64_t ad0 = smem_desc_sw128(0, HW * 128);
+        const uint32_t a_lo0 = (uint32_t)ad0, a_hi = (uint32_t)(ad0 >> 32);
+        const bool tr = a.trace != nullptr && el;
+        long long tr_te = 0, tr_full = 0, tr_issue = 0;
+        int it = 0;
+        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it++) {
+            const int s = it % NA, b = it & 1;
+            const long long t0 = tr ? clock64() : 0;
+            mbar_wait(BAR(B_TEMPTY + b), ((it >> 1) & 1) ^ 1);   // accumulator drained by the epilogue
+            const long long t1 = tr ? clock64() : 0;
+            mbar_wait(BAR(B_FULL_A + s), (it / NA) & 1);         // operand tile landed
+            const long long t2 = tr ? clock64() : 0;
+            fence_after_sync();
+            const uint32_t a_lo = a_lo0 | ((smem_u32(smem + OFF_A + s * A_STAGE) & 0x3FFFFu) >> 4);
+            const uint32_t d0 = tmem_base + b * 64;
+#pragma unroll
+            for (int tap = 0; tap < 9; tap++) {
+                const int dy = tap / 3, dx = tap % 3;            // halo coordinates of the tap
+#pragma unroll
+                for (int j = 0; j < 4; j++) {                    // K = 64 input channels = 4 x 16
+                    const uint64_t bd = ((uint64_t)b_hi << 32) | (b_lo + (tap * B_TAP + j * 2 * 1024) / 16);
+                    const uint64_t ad = ((uint64_t)a_hi << 32) | (a_lo + (dy * HW + dx) * 8 + j * 2);
+                    mma_ss_el(d0, ad, bd, IDESC, (tap | j) != 0, el);
+                }
+            }
+            if (el) {
+                mma_commit(BAR(B_EMPTY_A + s));
+                mma_commit(BAR(B_TFULL + b));
+            }
+            __syncwarp();
+            if (tr) { tr_te += t1 - t0; tr_full += t2 - t1; tr_issue += clock64() - t2; }
+        }
+        if (tr) {
+            atomicAdd(a.trace + 2, (unsigned long long)tr_te); atomicAdd(a.trace + 3, (unsigned long long)tr_full);
+            atomicAdd(a.trace + 4, (unsigned long long)tr_issue); atomicAdd(a.trace + 8, (unsigned long long)it);
+        }
+    } else {
+        // ===== epilogue: warps 0-3 take even tiles (accumulator 0), warps 4-7 odd tiles (accumulator 1) =====
+        const int set = warp >> 2, wq = warp & 3;
+        uint8_t *stg = smem + OFF_EPI + warp * EPI_WARP;
+        float acc0[8], acc1[8];
+        EpiCoef cf;
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            acc0[j] = acc1[j] = 0.0f;
+            const int c = (lane & 7) * 8 + j;
+            cf.sc[j] = EPI == EPI_DGRAD_BN ? a.p_scale[c] : 1.0f;
+            cf.sh[j] = EPI == EPI_DGRAD_BN ? a.p_shift[c] : 0.0f;
+            cf.mu[j] = EPI == EPI_DGRAD_BN ? a.p_mean[c] : 0.0f;
+            cf.is[j] = EPI == EPI_DGRAD_BN ? a.p_invstd[c] : 1.0f;
+        }
+        const bool tr = a.trace != nullptr && threadIdx.x == 0;
+        long long tr_wait = 0, tr_work = 0;
+        const long long tr_start = tr ? clock64() : 0;
+        int it = set, ntr = 0;
+        for (int tile = blockIdx.x + set * gridDim.x; tile < ntiles; tile += 2 * gridDim.x, it += 2) {
+            const int sz = it % NZ;
+            const int ty = (tile / a.tiles_x) * TH, tx = (tile % a.tiles_x) * TW;
+            const long long t0 = tr ? clock64() : 0;
+            mbar_wait(BAR(B_TFULL + set), (it >> 1) & 1);
+            const long long t1 = tr ? clock64() : 0;
+            fence_after_sync();
+            epilogue_tile<EPI>(a, tmem_base + ((uint32_t)(wq * 32) << 16) + set * 64, stg, smem + OFF_Z + sz * Z_STAGE,
+                               BAR(B_FULL_Z + sz), (it / NZ) & 1, lane, wq, ty, tx, acc0, acc1, cf);
+            if (DGRAD && lane == 0) mbar_arrive(BAR(B_EMPTY_Z + sz));
+            fence_before_sync();
+            mbar_arrive(BAR(B_TEMPTY + set));
+            if (tr) { tr_wait += t1 - t0; tr_work += clock64() - t1; ntr++; }
+        }
+        if (tr) {
+            atomicAdd(a.trace + 5, (unsigned long long)tr_wait); atomicAdd(a.trace + 6, (unsigned long long)tr_work);
+            atomicAdd(a.trace + 7, (unsigned long long)(clock64() - tr_start)); atomicAdd(a.trace + 9, (unsigned long long)ntr);
+        }
+        if ((EPI == EPI_STATS || EPI == EPI_DGRAD_BN) && a.stats) {
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                acc0[j] += __shfl_xor_sync(0xffffffffu, acc0[j], 8);
+                acc0[j] += __shfl_xor_sync(0xffffffffu, acc0[j], 16);
+                acc1[j] += __shfl_xor_sync(0xffffffffu, acc1[j], 8);
+                acc1[j] += __shfl_xor_sync(0xffffffffu, acc1[j], 16);
+            }
+            if (lane < 8) {
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    atomicAdd(a.stats + lane * 8 + j, (double)acc0[j]);
+                    atomicAdd(a.stats + 64 + lane * 8 + j, (double)acc1[j]);
+                }
+            }
+        }
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (warp == MMA_WARP) tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+// NHWC BF16 image [H][W][64] as a 3-D tensor (channels, x, y), 128-byte swizzle, box = boxw x boxh pixels
+static int make_tensor_map(CUtensorMap *m, const void *base, int H, int W, int boxw, int boxh)
+{
+    const cuuint64_t dims[3] = {64, (cuuint64_t)W, (cuuint64_t)H};
+    const cuuint64_t strides[2] = {128, (cuuint64_t)W * 128};
+    const cuuint32_t box[3] = {64, (cuuint32_t)boxw, (cuuint32_t)boxh};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    const CUresult r = cuTensorMapEncodeTiled(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void *>(base), dims, strides, box,
+                                              estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                              CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled failed (%d) for a %dx%d image at %p", (int)r, W, H, base);
+        return F2F_ECUDA;
+    }
+    return F2F_OK;
+}
+
+template <int EPI>
+static int launch_conv64t(ConvArgs a, cudaStream_t st)
+{
+    static bool configured = false;
+    if (!configured) {
+        F2F_CUDA_CHECK(cudaFuncSetAttribute(k_conv64t<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        configured = true;
+    }
+    a.tiles_x = cdiv(a.W, TW);
+    a.tiles_y = cdiv(a.H, TH);
+    CUtensorMap tm_in, tm_z;
+    int rc = make_tensor_map(&tm_in, a.in, a.H, a.W, HW, HH);
+    if (rc) return rc;
+    constexpr bool DGRAD = EPI == EPI_DGRAD_BN || EPI == EPI_DGRAD_RELU;
+    rc = make_tensor_map(&tm_z, DGRAD ? (const void *)a.zprev : (const void *)a.in, a.H, a.W, TW, TH);
+    if (rc) return rc;
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int ntiles = a.tiles_x * a.tiles_y;
+    const int grid = ntiles < sms ? ntiles : sms;
+    prof_begin(0, st);
+    k_conv64t<EPI><<<grid, NTHREADS, SMEM_BYTES, st>>>(a, tm_in, tm_z);
+    prof_end(0, st);
+    g_dncnn_launches++;
+    F2F_LAUNCH_CHECK();
+    return F2F_OK;
+}
+}  // namespace dnt
+
+namespace dn {
 
 // Weight layout transform: PyTorch conv weight [oc][ic][3][3] fp32 -> the smem image of B for
 //   forward (transpose = 0): B_tap[n = oc][k = ic] = w[oc][ic][tap]
@@ -445,6 +834,8 @@ void f2f_profile_dncnn_read(double out[4])
     }
 }
 
+void f2f_dncnn_set_trace(unsigned long long *d_counters) { g_conv_trace = d_counters; }
+
 int f2f_dncnn_prep_w64(const float *d_w, void *d_wprep, int transpose, void *stream)
 {
     if (!d_w || !d_wprep) { set_error("f2f_dncnn_prep_w64: bad arguments"); return F2F_EINVAL; }
@@ -462,12 +853,13 @@ int f2f_dncnn_conv64(const void *d_in, void *d_out, const void *d_wprep, const f
     a.in = (const bf16 *)d_in; a.out = (bf16 *)d_out; a.wprep = (const bf16 *)d_wprep;
     a.scale = d_scale; a.shift = d_shift; a.stats = d_stats;
     a.H = H; a.W = W; a.tiles_x = cdiv(W, TW); a.tiles_y = cdiv(H, TH);
+    a.trace = g_conv_trace;
     cudaStream_t st = (cudaStream_t)stream;
     const bool bn = d_scale != nullptr;
     if (bn && d_stats) return launch_conv64<PRO_BN_RELU, EPI_STATS>(a, st);
     if (bn) return launch_conv64<PRO_BN_RELU, EPI_STORE>(a, st);
-    if (d_stats) return launch_conv64<PRO_RAW, EPI_STATS>(a, st);
-    return launch_conv64<PRO_RAW, EPI_STORE>(a, st);
+    if (d_stats) return f2f::dnt::launch_conv64t<EPI_STATS>(a, st);
+    return f2f::dnt::launch_conv64t<EPI_STORE>(a, st);
 }
 
 int f2f_dncnn_dgrad64(const void *d_dz, void *d_gout, const void *d_wprep_t, const void *d_zprev, const float *d_pscale,
@@ -480,9 +872,10 @@ int f2f_dncnn_dgrad64(const void *d_dz, void *d_gout, const void *d_wprep_t, con
     a.zprev = (const bf16 *)d_zprev; a.p_scale = d_pscale; a.p_shift = d_pshift; a.p_mean = d_pmean; a.p_invstd = d_pinvstd;
     a.stats = d_stats;
     a.H = H; a.W = W; a.tiles_x = cdiv(W, TW); a.tiles_y = cdiv(H, TH);
+    a.trace = g_conv_trace;
     cudaStream_t st = (cudaStream_t)stream;
-    if (d_pscale) return launch_conv64<PRO_RAW, EPI_DGRAD_BN>(a, st);
-    return launch_conv64<PRO_RAW, EPI_DGRAD_RELU>(a, st);
+    if (d_pscale) return f2f::dnt::launch_conv64t<EPI_DGRAD_BN>(a, st);
+    return f2f::dnt::launch_conv64t<EPI_DGRAD_RELU>(a, st);
 }
 
 }  // extern "C"

@@ -424,7 +424,7 @@ struct Args {
 __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a)
 {
     extern __shared__ __align__(1024) uint8_t smem[];
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // provably warp-uniform
     const int ntiles = a.tiles_x * a.tiles_y;
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + OFF_BAR);
     const uint32_t bar0 = smem_u32(bars);
@@ -578,30 +578,34 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a)
             mbar_arrive(BAR(s));
         }
     } else {
-        // ===== MMA issuer =====
-        if (lane == 0) {
-            constexpr uint32_t IDESC = idesc_bf16(128, 64, 1, 1);
-            int it = 0;
-            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it++) {
-                const int s = it & 1;
-                mbar_wait(BAR(s), (it >> 1) & 1);
-                fence_after_sync();
-                const uint32_t a_base = smem_u32(smem + s * STAGE);
-                const uint32_t d_base = a_base + A_BYTES;
-#pragma unroll 1
-                for (int r = 0; r < 16; r++) {
-                    const uint64_t bd = smem_desc(d_base + r * D_R, 128, D_S);
+        // ===== MMA issuer: converged warp, the elected lane issues (see dncnn.cu) =====
+        const uint32_t el = elect_one();
+        constexpr uint32_t IDESC = idesc_bf16(128, 64, 1, 1);
+        // descriptors differ only in the start-address field (low word, 16-byte units)
+        const uint64_t ad0 = smem_desc(0, 128, A_S), bd0 = smem_desc(0, 128, D_S);
+        const uint32_t a_hi = (uint32_t)(ad0 >> 32), b_hi = (uint32_t)(bd0 >> 32);
+        int it = 0;
+        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it++) {
+            const int s = it & 1;
+            mbar_wait(BAR(s), (it >> 1) & 1);
+            fence_after_sync();
+            const uint32_t a_base = smem_u32(smem + s * STAGE);
+            const uint32_t a_lo = (uint32_t)ad0 | ((a_base & 0x3FFFFu) >> 4);
+            const uint32_t b_lo = (uint32_t)bd0 | (((a_base + A_BYTES) & 0x3FFFFu) >> 4);
 #pragma unroll
-                    for (int j = 0; j < 6; j++) {
-                        const int dy = j < 3 ? 0 : 2, dx = j % 3;
-                        const uint64_t ad = smem_desc(a_base + (r + dy) * A_R + dx * 16, 128, A_S);
-                        mma_ss(tmem_base + j * 64, ad, bd, IDESC, (it | r) != 0);
-                    }
+            for (int r = 0; r < 16; r++) {
+                const uint64_t bd = ((uint64_t)b_hi << 32) | (b_lo + r * (D_R / 16));
+#pragma unroll
+                for (int j = 0; j < 6; j++) {
+                    const int dy = j < 3 ? 0 : 2, dx = j % 3;
+                    const uint64_t ad = ((uint64_t)a_hi << 32) | (a_lo + (r + dy) * (A_R / 16) + dx);
+                    mma_ss_el(tmem_base + j * 64, ad, bd, IDESC, (it | r) != 0, el);
                 }
-                mma_commit(BAR(2 + s));
             }
-            mma_commit(BAR(4));
+            if (el) mma_commit(BAR(2 + s));
+            __syncwarp();
         }
+        if (el) mma_commit(BAR(4));
         __syncwarp();
     }
     fence_before_sync();

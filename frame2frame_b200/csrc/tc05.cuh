@@ -57,6 +57,20 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst_smem, const void *src, uin
                  : "memory");
 }
 
+// 3-D tiled tensor load global -> shared through a CUtensorMap (TMA), completion on an mbarrier;
+// coordinates are signed, elements outside the tensor are zero-filled
+__device__ __forceinline__ void tma_load_3d(uint32_t dst_smem, const void *tmap, uint32_t bar, int c0, int c1, int c2)
+{
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+        ::"r"(dst_smem), "l"(tmap), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const void *tmap)
+{
+    asm volatile("prefetch.tensormap [%0];" ::"l"(tmap) : "memory");
+}
+
 // ------------------------------------------------------------------- TMEM
 __device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols)
 {
@@ -101,6 +115,18 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo_bytes,
            ((uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32) | (1ull << 46);
 }
 
+// K-major operand in the 128-byte-swizzled layout a TMA tensor load writes (rows of 128 B, 16-byte
+// chunk c of row r stored at chunk c ^ (r & 7), phase taken from the absolute shared address):
+// 8 rows of a core-matrix group are consecutive 128-byte rows, SBO = stride between groups.  The
+// start address may be ANY multiple of 128 B inside such a region and SBO any multiple of 128 B
+// (measured: tools/ubench_mma.cu mode 2), which is what makes filter taps plain shifted views.
+// K advances by 32 B (16 BF16) inside the swizzled row.
+__device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t addr, uint32_t sbo_bytes)
+{
+    return (uint64_t)((addr & 0x3FFFFu) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32) |
+           (1ull << 46) | (2ull << 61);
+}
+
 // Instruction descriptor for kind::f16, BF16 x BF16 -> F32:
 //   c_format F32 = 1 @ bit 4, a_format BF16 = 1 @ bit 7, b_format BF16 = 1 @ bit 10,
 //   a_major @ bit 15, b_major @ bit 16 (0 = K-major, 1 = MN-major), N>>3 @ bit 17, M>>4 @ bit 24.
@@ -118,6 +144,21 @@ __device__ __forceinline__ void mma_ss(uint32_t d_tmem, uint64_t adesc, uint64_t
         "setp.ne.b32 p, %4, 0;\n\t"
         "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
         ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// The same, issued from a CONVERGED warp: every lane executes the instruction stream, the lane
+// with `elected` != 0 (elect_one()) issues.  Keeping the warp converged lets ptxas hold the
+// descriptors in uniform registers and drop the per-instruction elect loop it otherwise wraps
+// around tcgen05.mma in single-thread code (measured: 72 -> ~32 cycles per M128 N64 K16 issue).
+__device__ __forceinline__ void mma_ss_el(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate,
+                                          uint32_t elected)
+{
+    asm volatile(
+        "{\n\t.reg .pred p, q;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "setp.ne.b32 q, %5, 0;\n\t"
+        "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(elected)
         : "memory");
 }
 // all MMAs issued so far by this thread -> arrive on an mbarrier when they have completed

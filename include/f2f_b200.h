@@ -211,6 +211,12 @@ void f2f_dncnn_workspace_layout(int B, int H, int W, int train, size_t out[8]);
  * backward, slot 2(k-1)+1 = dz_k, slot 30 = g_0), so each backward kernel can be checked against
  * the reference formula on its own inputs.  NULL switches it off. */
 void f2f_dncnn_set_debug_dump(void *d_buf);
+/* Development aid: when d_counters != NULL (16 device uint64, zeroed by the caller), the 64->64
+ * convolution / input-gradient kernels add per-role SM-cycle totals over all CTAs: [0],[1] operand
+ * producer waiting for a free slot / staging a tile (one thread of group 0); [2],[3],[4] MMA
+ * issuer waiting for a drained accumulator / a staged tile / issuing; [5],[6] epilogue waiting for
+ * accumulators / draining a tile; [7] epilogue loop total; [8] tiles.  NULL switches it off. */
+void f2f_dncnn_set_trace(unsigned long long *d_counters);
 int f2f_dncnn_forward(const float *d_params, float *d_bn_running, long long *d_nbt,
                       const float *d_x, float *d_y, void *d_ws, size_t ws_bytes, int B, int H,
                       int W, int train, int residual, void *stream);

@@ -1,0 +1,259 @@
+// ubench_mma.cu -- development microbenchmark (not part of the library): issue rate and
+// correctness of tcgen05.mma M128 N64 K16 (BF16) for the operand layouts considered for the
+// 3x3 implicit-GEMM convolution, where the nine filter taps are shifted views of ONE haloed
+// 18x18-pixel activation tile in shared memory.
+//   mode 0  A, B "interleaved" (SWIZZLE_NONE) core matrices, chunk-planar tile (dncnn.cu as of r01a)
+//   mode 1  as 0 but every A view 128-B aligned (no tap shift): isolates the misalignment cost
+//   mode 2  A pixel-major 128-B rows, SWIZZLE_128B (what a TMA tensor load writes), taps = views
+//           starting at any 128-B row; B SWIZZLE_128B K-major
+//   mode 3  as 2 but every view 1024-B aligned, SBO 1024 (plain GEMM): reference rate
+//   mode 4  as 2 with descriptor base_offset = (start >> 7) & 7
+// build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o ubench_mma tools/ubench_mma.cu
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+#include "../frame2frame_b200/csrc/tc05.cuh"
+
+using namespace tc05;
+typedef __nv_bfloat16 bf16;
+
+constexpr int HWD = 18, HPIX = 324;
+constexpr int CH_STRIDE = (HPIX + 1) * 16;
+constexpr int A_BYTES = 42 * 1024;
+constexpr int B_TAP = 8192;
+constexpr int SMEM = 200 * 1024;
+
+__host__ __device__ inline int aval(int p, int c) { return ((p * 7 + c * 3) % 13) - 6; }
+__host__ __device__ inline int bval(int t, int n, int k) { return ((t * 5 + n * 3 + k) % 7) - 3; }
+
+__device__ __forceinline__ uint64_t desc_sw128(uint32_t addr, uint32_t sbo, uint32_t base_off)
+{
+    return (uint64_t)((addr & 0x3FFFFu) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)((sbo >> 4) & 0x3FFFu) << 32) | (1ull << 46) |
+           ((uint64_t)(base_off & 7u) << 49) | (2ull << 61);
+}
+
+__global__ void __launch_bounds__(128, 1) k_bench(int mode, int reps, float *out, long long *cycles, int N)
+{
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint8_t *A = smem, *B = smem + A_BYTES;
+    uint64_t *bar = (uint64_t *)(smem + A_BYTES + 9 * B_TAP);
+    uint32_t *tmem_ptr = (uint32_t *)(bar + 2);
+    const bool sw = mode >= 2;
+    for (int i = threadIdx.x; i < HPIX * 64; i += blockDim.x) {
+        const int p = i / 64, c = i % 64;
+        const size_t off = sw ? (size_t)p * 128 + (((c >> 3) ^ (p & 7)) << 4) + (c & 7) * 2
+                              : (size_t)(c >> 3) * CH_STRIDE + (size_t)p * 16 + (c & 7) * 2;
+        *(bf16 *)(A + off) = __float2bfloat16((float)aval(p, c));
+    }
+    for (int i = threadIdx.x; i < 9 * 64 * 64; i += blockDim.x) {
+        const int t = i / 4096, n = (i / 64) % 64, k = i % 64;
+        const size_t off = sw ? (size_t)t * B_TAP + n * 128 + (((k >> 3) ^ (n & 7)) << 4) + (k & 7) * 2
+                              : (size_t)t * B_TAP + (k >> 3) * 1024 + n * 16 + (k & 7) * 2;
+        *(bf16 *)(B + off) = __float2bfloat16((float)bval(t, n, k));
+    }
+    if (threadIdx.x == 0) { mbar_init(smem_u32(bar), 1); mbar_fence_init(); }
+    if (threadIdx.x < 32) tmem_alloc(smem_u32(tmem_ptr), 512);
+    fence_proxy_async();
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem = *tmem_ptr;
+    if (threadIdx.x < 32) {
+        const uint32_t el = elect_one();
+        const uint32_t IDESC = idesc_bf16(128, N, 0, 0);
+        const uint32_t a_base = smem_u32(A), b_base = smem_u32(B);
+        // descriptors: only the low word (start address >> 4) changes between MMAs
+        uint64_t a0, b0;
+        uint32_t a_tapy, a_tapx, a_h, a_j, b_tap, b_j;
+        if (mode <= 1) {
+            a0 = smem_desc(a_base, CH_STRIDE, mode == 0 ? HWD * 16 : 256);
+            b0 = smem_desc(b_base, 1024, 128);
+            a_tapy = mode == 0 ? HWD : 0; a_tapx = mode == 0 ? 1 : 0; a_h = 8; a_j = 2 * CH_STRIDE / 16; b_tap = B_TAP / 16; b_j = 128;
+        } else {
+            a0 = desc_sw128(a_base, mode == 3 ? 2048 : HWD * 128, 0);
+            b0 = desc_sw128(b_base, 1024, 0);
+            a_tapy = mode == 3 ? 0 : HWD * 8; a_tapx = mode == 3 ? 0 : 8; a_h = 64; a_j = 2; b_tap = B_TAP / 16; b_j = 2;
+        }
+        const uint32_t a_lo = (uint32_t)a0, a_hi = (uint32_t)(a0 >> 32), b_lo = (uint32_t)b0, b_hi = (uint32_t)(b0 >> 32);
+        const long long t0 = clock64();
+        for (int rep = 0; rep < reps; rep++) {
+#pragma unroll
+            for (int tap = 0; tap < 9; tap++) {
+                const int dy = tap / 3, dx = tap % 3;
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const uint64_t bd = ((uint64_t)b_hi << 32) | (b_lo + tap * b_tap + j * b_j);
+#pragma unroll
+                    for (int h = 0; h < 2; h++) {
+                        const uint64_t ad = ((uint64_t)a_hi << 32) | (a_lo + dy * a_tapy + dx * a_tapx + h * a_h + j * a_j);
+                        mma_ss_el(tmem + h * N, ad, bd, IDESC, (rep | tap | j) != 0, el);
+                    }
+                }
+            }
+        }
+        if (el) mma_commit(smem_u32(bar));
+        __syncwarp();
+        mbar_wait(smem_u32(bar), 0);
+        const long long t1 = clock64();
+        if (cycles && threadIdx.x == 0) cycles[blockIdx.x] = t1 - t0;
+    }
+    __syncthreads();
+    fence_after_sync();
+    if (out && blockIdx.x == 0) {
+        const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+        for (int part = 0; part < 4; part++) {
+            uint32_t r[32];
+            tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + part * 32, r);
+            tmem_ld_wait();
+            for (int q = 0; q < 32; q++) out[(size_t)(warp * 32 + lane) * 128 + part * 32 + q] = __uint_as_float(r[q]);
+        }
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (threadIdx.x < 32) tmem_dealloc(tmem, 512);
+}
+
+void issue_variants(long long *d_cyc);
+
+int main()
+{
+    cudaFuncSetAttribute(k_bench, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
+    float *d_out;
+    long long *d_cyc;
+    cudaMalloc(&d_out, 128 * 128 * 4);
+    cudaMalloc(&d_cyc, 148 * 8);
+    std::vector<float> out(128 * 128);
+    std::vector<long long> cyc(148);
+    for (int mode = 0; mode <= 3; mode++) {
+        // correctness, one pass of the 72 MMAs
+        cudaMemset(d_out, 0, 128 * 128 * 4);
+        k_bench<<<1, 128, SMEM>>>(mode, 1, d_out, nullptr, 64);
+        cudaError_t e = cudaDeviceSynchronize();
+        if (e != cudaSuccess) { printf("mode %d: %s\n", mode, cudaGetErrorString(e)); return 1; }
+        cudaMemcpy(out.data(), d_out, 128 * 128 * 4, cudaMemcpyDeviceToHost);
+        long bad = 0;
+        double maxerr = 0;
+        const bool shifted = mode == 0 || mode == 2 || mode == 4;
+        for (int h = 0; h < 2; h++)
+            for (int m = 0; m < 128; m++)
+                for (int n = 0; n < 64; n++) {
+                    const int g = m / 8, r = m % 8;
+                    double ref = 0;
+                    for (int tap = 0; tap < 9; tap++) {
+                        const int dy = tap / 3, dx = tap % 3;
+                        int p;
+                        if (shifted) p = (g + dy) * HWD + r + 8 * h + dx;
+                        else if (mode == 1) p = g * 16 + h * 8 + r;      // SBO 256 B = 16 pixels
+                        else p = g * 16 + h * 8 + r;                     // mode 3: SBO 2048 B = 16 rows of 128 B
+                        for (int k = 0; k < 64; k++) ref += (double)aval(p, k) * bval(tap, n, k);
+                    }
+                    const double d = fabs(ref - out[(size_t)m * 128 + h * 64 + n]);
+                    if (d > maxerr) maxerr = d;
+                    if (d > 0.5) bad++;
+                }
+        // timing on all SMs
+        const int reps = 40;
+        k_bench<<<148, 128, SMEM>>>(mode, reps, nullptr, d_cyc, 64);
+        cudaDeviceSynchronize();
+        k_bench<<<148, 128, SMEM>>>(mode, reps, nullptr, d_cyc, 64);
+        e = cudaDeviceSynchronize();
+        if (e != cudaSuccess) { printf("mode %d timing: %s\n", mode, cudaGetErrorString(e)); return 1; }
+        cudaMemcpy(cyc.data(), d_cyc, 148 * 8, cudaMemcpyDeviceToHost);
+        double avg = 0;
+        for (int i = 0; i < 148; i++) avg += cyc[i];
+        avg /= 148;
+        printf("mode %d: mismatches %ld (max err %.1f)   %.1f cycles per MMA (M128 N64 K16), %.0f per 72-MMA tile\n", mode, bad,
+               maxerr, avg / (reps * 72), avg / reps);
+    }
+    issue_variants(d_cyc);
+    for (int N = 16; N <= 256; N *= 2) {
+        const int reps = 40;
+        k_bench<<<148, 128, SMEM>>>(3, reps, nullptr, d_cyc, N);
+        cudaDeviceSynchronize();
+        k_bench<<<148, 128, SMEM>>>(3, reps, nullptr, d_cyc, N);
+        cudaError_t e = cudaDeviceSynchronize();
+        if (e != cudaSuccess) { printf("N %d timing: %s\n", N, cudaGetErrorString(e)); return 1; }
+        cudaMemcpy(cyc.data(), d_cyc, 148 * 8, cudaMemcpyDeviceToHost);
+        double avg = 0;
+        for (int i = 0; i < 148; i++) avg += cyc[i];
+        avg /= 148;
+        printf("mode 3, N = %3d: %.1f cycles per MMA (floor %d)\n", N, avg / (reps * 72), N / 2);
+    }
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Issue-rate variants (timing only): how cheaply can 72 M128 N64 K16 MMAs with different operand
+// views be issued?  VAR 0: one thread (threadIdx.x == 0).  VAR 1: converged warp, predicated on
+// elect.  VAR 2: one elected thread of warp 0 (if (elect_one())).
+template <int VAR>
+__global__ void __launch_bounds__(128, 1) k_issue(int reps, long long *cycles)
+{
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint64_t *bar = (uint64_t *)(smem + A_BYTES + 9 * B_TAP);
+    uint32_t *tmem_ptr = (uint32_t *)(bar + 2);
+    for (int i = threadIdx.x; i < (A_BYTES + 9 * B_TAP) / 16; i += blockDim.x) ((uint4 *)smem)[i] = make_uint4(0, 0, 0, 0);
+    if (threadIdx.x == 0) { mbar_init(smem_u32(bar), 1); mbar_fence_init(); }
+    if (threadIdx.x < 32) tmem_alloc(smem_u32(tmem_ptr), 128);
+    fence_proxy_async();
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem = *tmem_ptr;
+    constexpr uint32_t IDESC = idesc_bf16(128, 64, 0, 0);
+    const uint64_t a0 = desc_sw128(smem_u32(smem), HWD * 128, 0), b0 = desc_sw128(smem_u32(smem + A_BYTES), 1024, 0);
+    const uint32_t a_lo = (uint32_t)a0, a_hi = (uint32_t)(a0 >> 32), b_lo = (uint32_t)b0, b_hi = (uint32_t)(b0 >> 32);
+    const int warp_u = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);   // provably warp-uniform (CUTLASS canonical_warp_idx_sync)
+    if (warp_u == 0) {
+        const uint32_t el = elect_one();
+      if (VAR == 1 || el) {
+        const long long t0 = clock64();
+        for (int rep = 0; rep < reps; rep++) {
+#pragma unroll
+            for (int tap = 0; tap < 9; tap++) {
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const uint64_t bd = ((uint64_t)b_hi << 32) | (b_lo + tap * (B_TAP / 16) + j * 2);
+#pragma unroll
+                    for (int h = 0; h < 2; h++) {
+                        const uint64_t ad = ((uint64_t)a_hi << 32) | (a_lo + ((tap / 3) * HWD + tap % 3) * 8 + h * 64 + j * 2);
+                        if (VAR == 1) mma_ss_el(tmem + h * 64, ad, bd, IDESC, (rep | tap | j) != 0, el);
+                        else mma_ss(tmem + h * 64, ad, bd, IDESC, (rep | tap | j) != 0);
+                    }
+                }
+            }
+        }
+        if (el) mma_commit(smem_u32(bar));
+        if (el) {
+            mbar_wait(smem_u32(bar), 0);
+            cycles[blockIdx.x] = clock64() - t0;
+        }
+      }
+        __syncwarp();
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (threadIdx.x < 32) tmem_dealloc(tmem, 128);
+}
+
+template <int VAR>
+static void run_issue(long long *d_cyc)
+{
+    cudaFuncSetAttribute(k_issue<VAR>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
+    std::vector<long long> cyc(148);
+    const int reps = 40;
+    for (int r = 0; r < 2; r++) { k_issue<VAR><<<148, 128, SMEM>>>(reps, d_cyc); cudaDeviceSynchronize(); }
+    cudaMemcpy(cyc.data(), d_cyc, 148 * 8, cudaMemcpyDeviceToHost);
+    double avg = 0;
+    for (int i = 0; i < 148; i++) avg += cyc[i];
+    printf("issue variant %d: %.1f cycles per MMA (%s)\n", VAR, avg / 148 / (reps * 72), cudaGetErrorString(cudaGetLastError()));
+}
+
+void issue_variants(long long *d_cyc)
+{
+    run_issue<0>(d_cyc);
+    run_issue<1>(d_cyc);
+}
