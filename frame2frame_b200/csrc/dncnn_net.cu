@@ -464,7 +464,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a)
             mbar_wait(BAR(2 + s), ((it >> 1) & 1) ^ 1);
             uint8_t *dstA = smem + s * STAGE;
             const int ty0 = (tile / a.tiles_x) * 16 - 1, tx0 = (tile % a.tiles_x) * 16 - 1;
-            constexpr int ROUNDS = (324 + 15) / 16, U = 7;
+            constexpr int ROUNDS = (324 + 15) / 16, U = ROUNDS;   // the whole tile's loads in flight at once (latency-bound otherwise)
             int pix = ptid >> 3;
 #pragma unroll 1
             for (int r0 = 0; r0 < ROUNDS; r0 += U) {
