@@ -222,7 +222,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="f2f", choices=["f2f", "tvl1"])
+    ap.add_argument("--workload", default="f2f", choices=["f2f", "tvl1", "batch"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-tvl1", action="store_true", help="f2f workload: skip the secondary TV-L1 measurement")
     args = ap.parse_args()
@@ -246,6 +246,8 @@ def main():
     try:
         if args.workload == "tvl1":
             line = ours_tvl1(args, rank, world, local_rank)
+        elif args.workload == "batch":
+            line = bench_f2f.ours_batch(args, rank, world, local_rank, ClockSampler, peaks)
         else:
             line = bench_f2f.ours(args, rank, world, local_rank, ClockSampler, peaks)
             if not args.no_tvl1:

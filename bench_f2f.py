@@ -194,8 +194,8 @@ def ours(args, rank, world, local_rank, ClockSampler, peaks):
         "gpu_launches": int(launches),
         "clocks": clocks,
         "model_tflops": frame_flop * value / world / 1e12,
-        "roofline": {"bound": "tensor", "kernel": "k_conv64 (tcgen05 implicit-GEMM 3x3 64->64 conv: forward and input-gradient "
-                                                  "launches)",
+        "roofline": {"bound": "tensor", "kernel": "k_conv64 / k_conv64t (tcgen05 implicit-GEMM 3x3 64->64 conv: the forward and "
+                                                  "input-gradient launches)",
                      "achieved": conv_tf, "peak": peak_tf, "peak_source": pk_kind + " bf16_tflops_sustained", "unit": "TFLOP/s",
                      "frac": conv_tf / peak_tf if conv_tf else None, "flop_per_launch": CONV64_FLOP_PER_PX * P,
                      "launches_per_step": conv_n / args.steps, "avg_launch_us": conv_ms * 1e3 / conv_n if conv_n else None,
@@ -207,3 +207,76 @@ def ours(args, rank, world, local_rank, ClockSampler, peaks):
     if world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline()
     return line
+
+
+def ours_batch(args, rank, world, local_rank, ClockSampler, peaks):
+    """BASELINE.json configs[3]: batch-mode F2F fine-tune over 8 sequences at 1080p, DnCNN gradients
+    all-reduced with NCCL (frame2frame_b200/batch_f2f.py).  A step = one frame of EVERY sequence:
+    warp + masks once per sequence, 20 x (per local sequence: train forward, masked L1, backward;
+    then ONE gradient all-reduce + BatchNorm-statistics all-gather + Adam), eval forward per
+    sequence.  Total work is fixed (8 sequences) -> strong scaling over 1/2/4/8 GPUs."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from frame2frame_b200 import _lib, synth
+    from frame2frame_b200.batch_f2f import BatchF2F
+    from frame2frame_b200.blind_denoising import load_network
+
+    NSEQ = 8
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    _lib.lib()
+    gold = os.path.join(os.path.dirname(os.path.abspath(__file__)), "tests", "golden", "dncnn_s25_synth.npz")
+    eng = BatchF2F(load_network(gold, dev), NSEQ)
+    nf = 3
+    frames = {s: [torch.from_numpy(f)[None, None].to(dev) for f in _frames(nf, s, synth)] for s in eng.local}
+    flow = torch.from_numpy(synth.backward_flow(H, W, 1))[None].to(dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step(k):
+        currs = [frames[s][(k + 1) % nf] for s in eng.local]
+        prevs = [frames[s][k % nf] for s in eng.local]
+        eng.finetune(currs, prevs, [flow] * len(currs), ITERS)
+        return [eng.denoise(c) for c in currs]
+
+    for k in range(args.warmup):
+        step(k)
+    barrier()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for k in range(args.steps):
+        step(args.warmup + k)
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop() if sampler else None
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max = float(t.item())
+    if rank != 0:
+        return
+    value = NSEQ * args.steps / (ms_max * 1e-3)
+    P = H * W
+    frame_flop = (ITERS * FLOP_PER_PX_TRAIN + FLOP_PER_PX_FWD) * P
+    pk, pk_kind = peaks()
+    peak_tf = pk.get("bf16_tflops_sustained", pk["bf16_tflops"])
+    tf = frame_flop * value / world / 1e12
+    return {
+        "metric": "batch-mode F2F fine-tuned frames/sec @1080p gray", "value": value, "unit": "frames/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_max / args.steps, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": "configs[3]: batch-mode F2F fine-tune, 8 sequences x 1080p gray sigma=25, iter=20 per frame, one "
+                               "Adam step per inner iteration on the summed loss; sequences sharded over ranks, flat 556032-float "
+                               "gradient all-reduced with NCCL, BatchNorm batch statistics all-gathered (ordered EMA)",
+                   "frame": "%dx%d" % (W, H), "iter": ITERS, "sequences": NSEQ,
+                   "l2": "inputs larger than L2 (265 MB per activation)"},
+        "clocks": clocks, "model_tflops_per_gpu": tf,
+        "roofline": {"bound": "tensor", "kernel": "whole train step (model FLOPs)", "achieved": tf, "peak": peak_tf,
+                     "peak_source": pk_kind + " bf16_tflops_sustained", "unit": "TFLOP/s", "frac": tf / peak_tf, "traffic": None},
+    }
