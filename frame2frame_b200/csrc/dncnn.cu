@@ -29,6 +29,7 @@
 //               once (the layer is within ~20% of being HBM-bound, so bytes in flight matter)
 //   warp  12    MMA issuer (72 tcgen05.mma per tile into a double-buffered accumulator) + TMEM owner
 #include <cuda.h>
+#include <stdlib.h>
 #include <vector>
 #include "f2f_common.cuh"
 #include "tc05.cuh"
@@ -113,6 +114,7 @@ struct ConvArgs {
 };
 
 unsigned long long *g_conv_trace = nullptr;
+bool g_conv_legacy = getenv("F2F_CONV_LEGACY") != nullptr;   // development switch, see f2f_dncnn_set_legacy
 
 // ------------------------------------------------------------------ producer
 // Stages one haloed tile: 324 pixels x 8 chunks of 16 B.  Thread t of the 128-thread group owns
@@ -459,22 +461,23 @@ constexpr int TW = 8, TH = 16;
 constexpr int HW = TW + 2, HH = TH + 2, HPIX = HW * HH;   // 10 x 18 = 180 pixels
 constexpr int A_TX = HPIX * 128;                           // bytes one operand load delivers
 constexpr int A_STAGE = 23 * 1024;                         // 23040 rounded up to the swizzle period
-constexpr int NA = 3;
+constexpr int NA_MAX = 5;   // operand ring: 3 stages next to the pre-activation ring (input gradient), else 5
 constexpr int Z_STAGE = TW * TH * 128;                     // 16384
 constexpr int NZ = 3;
 constexpr int B_TAP = 64 * 64 * 2, B_BYTES = 9 * B_TAP;
 constexpr int EPI_ROW = 144, EPI_WARP = 32 * EPI_ROW, NEPI = 8;
 constexpr int OFF_B = 0;
 constexpr int OFF_A = OFF_B + B_BYTES;
-constexpr int OFF_Z = OFF_A + NA * A_STAGE;
+constexpr int OFF_Z = OFF_A + 3 * A_STAGE;
 constexpr int OFF_EPI = OFF_Z + NZ * Z_STAGE;
 constexpr int OFF_BAR = OFF_EPI + NEPI * EPI_WARP;
 constexpr int SMEM_BYTES = OFF_BAR + 256 + 1024;           // + slack to align the base to 1024 B
-constexpr int NTHREADS = 11 * 32;
-constexpr int MMA_WARP = 8, TMA_A_WARP = 9, TMA_Z_WARP = 10;
+constexpr int NTHREADS_RAW = 11 * 32, NTHREADS_BN = 15 * 32;   // + four transform warps when the operand needs BN+ReLU
+constexpr int MMA_WARP = 8, TMA_A_WARP = 9, TMA_Z_WARP = 10, XF_WARP0 = 11;
 constexpr int TMEM_COLS = 128;
 // barrier slots
-constexpr int B_FULL_A = 0, B_EMPTY_A = 3, B_FULL_Z = 6, B_EMPTY_Z = 9, B_TFULL = 12, B_TEMPTY = 14, B_W = 16;
+constexpr int B_FULL_A = 0, B_EMPTY_A = 5, B_RAW_A = 10, B_FULL_Z = 15, B_EMPTY_Z = 18, B_TFULL = 21, B_TEMPTY = 23, B_W = 25;
+static_assert(NA_MAX * A_STAGE <= 3 * A_STAGE + NZ * Z_STAGE, "the 5-stage operand ring reuses the pre-activation ring's space");
 static_assert(SMEM_BYTES <= 232448, "shared memory budget");
 static_assert(OFF_A % 1024 == 0 && OFF_Z % 1024 == 0 && A_STAGE % 1024 == 0, "swizzle alignment");
 
@@ -551,10 +554,11 @@ __device__ __forceinline__ void epilogue_tile(const ConvArgs &a, uint32_t tmem_a
     __syncwarp();
 }
 
-template <int EPI>
-__global__ void __launch_bounds__(NTHREADS, 1) k_conv64t(ConvArgs a, const __grid_constant__ CUtensorMap tm_in,
-                                                         const __grid_constant__ CUtensorMap tm_z)
+template <int PRO, int EPI>
+__global__ void __launch_bounds__(PRO == dn::PRO_BN_RELU ? NTHREADS_BN : NTHREADS_RAW, 1)
+k_conv64t(ConvArgs a, const __grid_constant__ CUtensorMap tm_in, const __grid_constant__ CUtensorMap tm_z)
 {
+    constexpr bool XF = PRO == dn::PRO_BN_RELU;
     extern __shared__ uint8_t smem_raw[];
     // 1024-byte aligned base: the swizzle phase of a TMA-written row is then (row & 7)
     uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
@@ -563,11 +567,14 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv64t(ConvArgs a, const __gri
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + OFF_BAR);
     const uint32_t bar0 = smem_u32(bars);
     auto BAR = [&](int i) { return bar0 + 8u * i; };
-    uint32_t *tmem_ptr = reinterpret_cast<uint32_t *>(bars + 20);
+    uint32_t *tmem_ptr = reinterpret_cast<uint32_t *>(bars + 26);
     constexpr bool DGRAD = EPI == EPI_DGRAD_BN || EPI == EPI_DGRAD_RELU;
+    constexpr int NA = DGRAD ? 3 : NA_MAX;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < NA; s++) { mbar_init(BAR(B_FULL_A + s), 1); mbar_init(BAR(B_EMPTY_A + s), 1); }
+        for (int s = 0; s < NA; s++) {
+            mbar_init(BAR(B_FULL_A + s), XF ? 128 : 1); mbar_init(BAR(B_EMPTY_A + s), 1); mbar_init(BAR(B_RAW_A + s), 1);
+        }
         for (int s = 0; s < NZ; s++) { mbar_init(BAR(B_FULL_Z + s), 1); mbar_init(BAR(B_EMPTY_Z + s), 4); }
         for (int b = 0; b < 2; b++) { mbar_init(BAR(B_TFULL + b), 1); mbar_init(BAR(B_TEMPTY + b), 128); }
         mbar_init(BAR(B_W), 1);
@@ -592,8 +599,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv64t(ConvArgs a, const __gri
                 const long long t0 = tr ? clock64() : 0;
                 mbar_wait(BAR(B_EMPTY_A + s), ((it / NA) & 1) ^ 1);
                 if (tr) tr_wait += clock64() - t0;
-                mbar_arrive_expect_tx(BAR(B_FULL_A + s), A_TX);
-                tma_load_3d(smem_u32(smem + OFF_A + s * A_STAGE), &tm_in, BAR(B_FULL_A + s), 0, tx0, ty0);
+                const uint32_t landed = BAR((XF ? B_RAW_A : B_FULL_A) + s);   // with a transform, the MMA waits for IT
+                mbar_arrive_expect_tx(landed, A_TX);
+                tma_load_3d(smem_u32(smem + OFF_A + s * A_STAGE), &tm_in, landed, 0, tx0, ty0);
             }
             if (tr) atomicAdd(a.trace + 0, (unsigned long long)tr_wait);
         }
@@ -612,6 +620,48 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv64t(ConvArgs a, const __gri
             }
         }
         __syncwarp();
+    } else if (XF && warp >= XF_WARP0) {
+        // ===== operand transform, in place: a = relu(z * scale + shift), the BatchNorm + ReLU of the layer below
+        // (net.py:17-18).  Pixels outside the image stay 0: zero padding applies to the ACTIVATION. =====
+        const int xt = threadIdx.x - XF_WARP0 * 32, chunk = xt & 7;       // 128 threads; a thread keeps one channel chunk
+        float sc[8], sh[8];
+#pragma unroll
+        for (int j = 0; j < 8; j++) { sc[j] = a.scale[chunk * 8 + j]; sh[j] = a.shift[chunk * 8 + j]; }
+        int it = 0;
+        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it++) {
+            const int s = it % NA;
+            const int ty0 = (tile / a.tiles_x) * TH - 1, tx0 = (tile % a.tiles_x) * TW - 1;
+            uint8_t *st = smem + OFF_A + s * A_STAGE;
+            mbar_wait(BAR(B_RAW_A + s), (it / NA) & 1);
+            constexpr int ROUNDS = (HPIX + 15) / 16;                      // 16 pixels per round of 128 threads
+            uint4 v[ROUNDS];
+            uint32_t ok = 0;
+#pragma unroll
+            for (int u = 0; u < ROUNDS; u++) {
+                const int pix = (xt >> 3) + 16 * u;
+                const int gy = ty0 + pix / HW, gx = tx0 + pix % HW;
+                if (pix < HPIX && gy >= 0 && gy < a.H && gx >= 0 && gx < a.W) {
+                    ok |= 1u << u;
+                    v[u] = *reinterpret_cast<const uint4 *>(st + pix * 128 + ((chunk ^ (pix & 7)) << 4));
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < ROUNDS; u++) {
+                if ((ok >> u) & 1u) {
+                    const int pix = (xt >> 3) + 16 * u;
+                    uint32_t w[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        const float2 f = unpack_bf16(w[j]);
+                        w[j] = pack_bf16(fmaxf(fmaf(f.x, sc[2 * j], sh[2 * j]), 0.0f),
+                                         fmaxf(fmaf(f.y, sc[2 * j + 1], sh[2 * j + 1]), 0.0f));
+                    }
+                    *reinterpret_cast<uint4 *>(st + pix * 128 + ((chunk ^ (pix & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+                }
+            }
+            fence_proxy_async();                                          // st.shared -> visible to the tensor core's reads
+            mbar_arrive(BAR(B_FULL_A + s));
+        }
     } else if (warp == MMA_WARP) {
         // ===== MMA issuer: the warp stays converged, the elected lane issues =====
         const uint32_t el = elect_one();
@@ -736,12 +786,12 @@ static int make_tensor_map(CUtensorMap *m, const void *base, int H, int W, int b
     return F2F_OK;
 }
 
-template <int EPI>
+template <int PRO, int EPI>
 static int launch_conv64t(ConvArgs a, cudaStream_t st)
 {
     static bool configured = false;
     if (!configured) {
-        F2F_CUDA_CHECK(cudaFuncSetAttribute(k_conv64t<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        F2F_CUDA_CHECK(cudaFuncSetAttribute(k_conv64t<PRO, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
         configured = true;
     }
     a.tiles_x = cdiv(a.W, TW);
@@ -758,7 +808,7 @@ static int launch_conv64t(ConvArgs a, cudaStream_t st)
     const int ntiles = a.tiles_x * a.tiles_y;
     const int grid = ntiles < sms ? ntiles : sms;
     prof_begin(0, st);
-    k_conv64t<EPI><<<grid, NTHREADS, SMEM_BYTES, st>>>(a, tm_in, tm_z);
+    k_conv64t<PRO, EPI><<<grid, PRO == dn::PRO_BN_RELU ? NTHREADS_BN : NTHREADS_RAW, SMEM_BYTES, st>>>(a, tm_in, tm_z);
     prof_end(0, st);
     g_dncnn_launches++;
     F2F_LAUNCH_CHECK();
@@ -835,6 +885,7 @@ void f2f_profile_dncnn_read(double out[4])
 }
 
 void f2f_dncnn_set_trace(unsigned long long *d_counters) { g_conv_trace = d_counters; }
+void f2f_dncnn_set_legacy(int on) { g_conv_legacy = on != 0; }
 
 int f2f_dncnn_prep_w64(const float *d_w, void *d_wprep, int transpose, void *stream)
 {
@@ -856,10 +907,14 @@ int f2f_dncnn_conv64(const void *d_in, void *d_out, const void *d_wprep, const f
     a.trace = g_conv_trace;
     cudaStream_t st = (cudaStream_t)stream;
     const bool bn = d_scale != nullptr;
-    if (bn && d_stats) return launch_conv64<PRO_BN_RELU, EPI_STATS>(a, st);
-    if (bn) return launch_conv64<PRO_BN_RELU, EPI_STORE>(a, st);
-    if (d_stats) return f2f::dnt::launch_conv64t<EPI_STATS>(a, st);
-    return f2f::dnt::launch_conv64t<EPI_STORE>(a, st);
+    if (g_conv_legacy) {       // the register-staged kernel (kept for comparison; f2f_dncnn_set_legacy)
+        if (bn && d_stats) return launch_conv64<PRO_BN_RELU, EPI_STATS>(a, st);
+        if (bn) return launch_conv64<PRO_BN_RELU, EPI_STORE>(a, st);
+    }
+    if (bn && d_stats) return f2f::dnt::launch_conv64t<PRO_BN_RELU, EPI_STATS>(a, st);
+    if (bn) return f2f::dnt::launch_conv64t<PRO_BN_RELU, EPI_STORE>(a, st);
+    if (d_stats) return f2f::dnt::launch_conv64t<PRO_RAW, EPI_STATS>(a, st);
+    return f2f::dnt::launch_conv64t<PRO_RAW, EPI_STORE>(a, st);
 }
 
 int f2f_dncnn_dgrad64(const void *d_dz, void *d_gout, const void *d_wprep_t, const void *d_zprev, const float *d_pscale,
@@ -874,8 +929,8 @@ int f2f_dncnn_dgrad64(const void *d_dz, void *d_gout, const void *d_wprep_t, con
     a.H = H; a.W = W; a.tiles_x = cdiv(W, TW); a.tiles_y = cdiv(H, TH);
     a.trace = g_conv_trace;
     cudaStream_t st = (cudaStream_t)stream;
-    if (d_pscale) return f2f::dnt::launch_conv64t<EPI_DGRAD_BN>(a, st);
-    return f2f::dnt::launch_conv64t<EPI_DGRAD_RELU>(a, st);
+    if (d_pscale) return f2f::dnt::launch_conv64t<PRO_RAW, EPI_DGRAD_BN>(a, st);
+    return f2f::dnt::launch_conv64t<PRO_RAW, EPI_DGRAD_RELU>(a, st);
 }
 
 }  // extern "C"

@@ -217,6 +217,9 @@ void f2f_dncnn_set_debug_dump(void *d_buf);
  * issuer waiting for a drained accumulator / a staged tile / issuing; [5],[6] epilogue waiting for
  * accumulators / draining a tile; [7] epilogue loop total; [8] tiles.  NULL switches it off. */
 void f2f_dncnn_set_trace(unsigned long long *d_counters);
+/* Development aid: on != 0 routes the BN+ReLU-prologue convolutions to the older register-staged
+ * kernel (dn::k_conv64) instead of the TMA-fed one with in-place transform warps, for comparison. */
+void f2f_dncnn_set_legacy(int on);
 int f2f_dncnn_forward(const float *d_params, float *d_bn_running, long long *d_nbt,
                       const float *d_x, float *d_y, void *d_ws, size_t ws_bytes, int B, int H,
                       int W, int train, int residual, void *stream);

@@ -20,6 +20,24 @@ def bf(t):
     return t.to(torch.bfloat16).to(torch.float32)
 
 
+# Which classes of tensors are rounded to BF16 (all of them = the CUDA path's data flow).  The
+# switches exist for tools/exp_bf16_parity.py, which attributes the end-to-end PSNR difference
+# against the FP32 oracle to weights / activations / gradients.
+ROUND = {"w": True, "act": True, "grad": True}
+
+
+def bfw(t):
+    return bf(t) if ROUND["w"] else t
+
+
+def bfa(t):
+    return bf(t) if ROUND["act"] else t
+
+
+def bfg(t):
+    return bf(t) if ROUND["grad"] else t
+
+
 def unpack(flat):
     """flat parameter vector (state_dict order) -> (w0, [(w_k, gamma_k, beta_k)]*15, w16)"""
     o = 0
@@ -39,12 +57,12 @@ def forward_backward(flat, x, dy=None, running=None, train=True, residual=True):
     w0, mid, w16 = unpack(flat.detach().float())
     x = x.float()
     n_el = float(x.shape[0] * x.shape[2] * x.shape[3])
-    a = [bf(F.relu(F.conv2d(x, w0, padding=1)))]
+    a = [bfa(F.relu(F.conv2d(x, w0, padding=1)))]
     z, coef = [None], [None]
     new_running = None if running is None else running.clone()
     for k in range(1, 16):
         w, gamma, beta = mid[k - 1]
-        zk = bf(F.conv2d(a[k - 1], bf(w), padding=1))
+        zk = bfa(F.conv2d(a[k - 1], bfw(w), padding=1))
         if train:
             zd = zk.double()
             mean = zd.mean((0, 2, 3))
@@ -62,7 +80,7 @@ def forward_backward(flat, x, dy=None, running=None, train=True, residual=True):
         yk = zk * scale.view(1, -1, 1, 1) + shift.view(1, -1, 1, 1)
         z.append(zk)
         coef.append((scale, shift, mean, invstd, yk > 0))
-        a.append(bf(F.relu(yk)) if k < 15 else F.relu(yk))   # the 64->1 layer consumes BN+ReLU of z_15 in FP32
+        a.append(bfa(F.relu(yk)) if k < 15 else F.relu(yk))   # the 64->1 layer consumes BN+ReLU of z_15 in FP32
     noise = F.conv2d(a[15], w16, padding=1)
     out = {"y": x - noise if residual else noise, "running": new_running}
     if dy is None:
@@ -71,7 +89,7 @@ def forward_backward(flat, x, dy=None, running=None, train=True, residual=True):
     grads = torch.zeros_like(flat, dtype=torch.float32)
     gw0, gmid, gw16 = unpack(grads)
     gw16.copy_(torch.nn.grad.conv2d_weight(a[15], w16.shape, dn, padding=1))
-    g = bf(torch.nn.grad.conv2d_input(a[15].shape, w16, dn, padding=1) * coef[15][4])
+    g = bfg(torch.nn.grad.conv2d_input(a[15].shape, w16, dn, padding=1) * coef[15][4])
     for k in range(15, 0, -1):
         w, gamma, beta = mid[k - 1]
         scale, shift, mean, invstd, _ = coef[k]
@@ -81,13 +99,13 @@ def forward_backward(flat, x, dy=None, running=None, train=True, residual=True):
         A = (gamma * invstd).double()
         Bc = -A * invstd.double() * dgamma / n_el
         Cc = A * (-dbeta / n_el + mean.double() * invstd.double() * dgamma / n_el)
-        dz = bf(A.float().view(1, -1, 1, 1) * g + (Bc.float().view(1, -1, 1, 1) * z[k] + Cc.float().view(1, -1, 1, 1)))
+        dz = bfg(A.float().view(1, -1, 1, 1) * g + (Bc.float().view(1, -1, 1, 1) * z[k] + Cc.float().view(1, -1, 1, 1)))
         gmid[k - 1][0].copy_(torch.nn.grad.conv2d_weight(a[k - 1], w.shape, dz, padding=1))
         gmid[k - 1][1].copy_(dgamma.float())
         gmid[k - 1][2].copy_(dbeta.float())
-        gin = torch.nn.grad.conv2d_input(a[k - 1].shape, bf(w), dz, padding=1)
+        gin = torch.nn.grad.conv2d_input(a[k - 1].shape, bfw(w), dz, padding=1)
         mask = coef[k - 1][4] if k >= 2 else (a[0] > 0)
-        g = bf(gin * mask)
+        g = bfg(gin * mask)
     gw0.copy_(torch.nn.grad.conv2d_weight(x, w0.shape, g, padding=1))
     out["grads"] = grads
     return out
