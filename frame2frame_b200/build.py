@@ -71,7 +71,7 @@ def build(force=False, verbose=False):
             raise RuntimeError("nvcc failed on %s: %s" % (u, " ".join(cmd)))
         if verbose:
             print(out)
-    cmd = [nvcc()] + ARCH + ["-shared", "-o", LIB] + objs + ["-lcuda"]
+    cmd = [nvcc()] + ARCH + ["-shared", "-o", LIB] + objs
     subprocess.check_call(cmd)
     return LIB
 

@@ -776,9 +776,24 @@ static int make_tensor_map(CUtensorMap *m, const void *base, int H, int W, int b
     const cuuint64_t strides[2] = {128, (cuuint64_t)W * 128};
     const cuuint32_t box[3] = {64, (cuuint32_t)boxw, (cuuint32_t)boxh};
     const cuuint32_t estr[3] = {1, 1, 1};
-    const CUresult r = cuTensorMapEncodeTiled(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void *>(base), dims, strides, box,
-                                              estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                                              CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    // the driver entry point is resolved through the runtime, so the library carries no link-time
+    // dependency on libcuda.so.1 (it must load, and export its symbols, on a machine without a driver)
+    typedef CUresult (*encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static encode_fn encode = nullptr;
+    if (!encode) {
+        void *fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) != cudaSuccess || !fn) {
+            set_error("cuTensorMapEncodeTiled is not available from the installed driver");
+            return F2F_ECUDA;
+        }
+        encode = (encode_fn)fn;
+    }
+    const CUresult r = encode(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void *>(base), dims, strides, box,
+                              estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                              CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
         set_error("cuTensorMapEncodeTiled failed (%d) for a %dx%d image at %p", (int)r, W, H, base);
         return F2F_ECUDA;
