@@ -17,6 +17,7 @@ ITERS = 20
 FLOP_PER_PX_FWD = 1108224
 FLOP_PER_PX_TRAIN = 3323520
 CONV64_FLOP_PER_PX = 2 * 9 * 64 * 64
+LOOKAHEAD = 16                     # frame pairs per batched TV-L1 call (OnlineF2F.run_sequence)
 FLOW_KW = dict(nscales=5)          # tvl1flow defaults of main.c:25-35 with the 5-scale pyramid of configs[1]
 METRIC = "F2F denoised frames/sec @1080p gray"
 
@@ -117,17 +118,25 @@ def ours(args, rank, world, local_rank, ClockSampler, peaks):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def step_device(k):
-        return engine.step_frame(devf[(k + 1) % nf], devf[k % nf], None, ITERS, flow_kw=FLOW_KW)
+    def run_device(k0, nsteps):
+        """nsteps frames of the online loop, frames resident in HBM; the backward flows of up to LOOKAHEAD
+        consecutive pairs are computed in one batched TV-L1 call inside this (timed) region."""
+        fr = [devf[(k0 + j) % nf] for j in range(nsteps + 1)]
+        den = None
+        for _, den in engine.run_sequence(fr, ITERS, lookahead=LOOKAHEAD, flow_kw=FLOW_KW):
+            pass
+        return den
 
-    def step_host(k):
-        curr = host[(k + 1) % nf].to(dev, non_blocking=True)       # H2D of this step's input from pinned memory
-        den = engine.step_frame(curr, devf[k % nf], None, ITERS, flow_kw=FLOW_KW)
-        out_host.copy_(den, non_blocking=True)                      # D2H of the step's result
+    def run_host(k0, nsteps):
+        """The same from pinned host frames to pinned host outputs: every frame is uploaded once (H2D) and every
+        denoised frame read back (D2H) inside the timed region."""
+        fr = [host[(k0 + j) % nf] for j in range(nsteps + 1)]
+        outs = [out_host] * (nsteps + 1)
+        for _ in engine.run_sequence(fr, ITERS, lookahead=LOOKAHEAD, flow_kw=FLOW_KW, out=outs):
+            pass
         torch.cuda.current_stream().synchronize()
 
-    for k in range(args.warmup):
-        step_device(k)
+    run_device(0, args.warmup)
     prof = (C.c_double * 5)()
     lib.f2f_profile_read(prof)
     launches_before = prof[4]
@@ -136,8 +145,7 @@ def ours(args, rank, world, local_rank, ClockSampler, peaks):
     sampler = ClockSampler(local_rank) if rank == 0 else None
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for k in range(args.steps):
-        den = step_device(args.warmup + k)
+    den = run_device(args.warmup, args.steps)
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1)
@@ -154,11 +162,10 @@ def ours(args, rank, world, local_rank, ClockSampler, peaks):
     value = world * args.steps / (ms_max * 1e-3)
 
     # ---- end to end: host frames in, denoised frame out, through OnlineF2F.step_frame ----
-    step_host(0)
+    run_host(0, 1)
     barrier()
     t0 = time.perf_counter()
-    for k in range(args.steps):
-        step_host(1 + k)
+    run_host(1, args.steps)
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
     t = torch.tensor([dt], dtype=torch.float64, device=dev)
@@ -183,13 +190,15 @@ def ours(args, rank, world, local_rank, ClockSampler, peaks):
         "dtype": "bf16", "data": "synthetic",
         "config": {"workload": "configs[2]: online F2F denoise, 1080p gray sigma=25 synthetic seq, DnCNN-25 layout "
                                "(weights pre-trained on synthetic textures: tests/golden/dncnn_s25_synth.npz), iter=20 per "
-                               "frame, TV-L1 backward flow computed on the device per frame; 1 frame per step per GPU, "
+                               "frame, TV-L1 backward flows computed on the device inside the timed region (up to %d consecutive "
+                               "pairs per batched call); 1 frame per step per GPU, " % LOOKAHEAD +
                                "ranks denoise independent chunks (no collective)",
                    "frame": "%dx%d" % (W, H), "iter": ITERS, "precision": "BF16 operands/activations, FP32 accumulate, "
                    "FP32 master weights, Adam and BatchNorm statistics",
                    "l2": "inputs larger than L2: every layer streams 265 MB activations (4.8 GB workspace per step)"},
         "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": H * W * 4, "d2h_bytes_per_step": H * W * 4,
-                "api": "OnlineF2F.step_frame (frame2frame_b200/blind_denoising.py) from/to pinned host frames",
+                "api": "OnlineF2F.run_sequence (frame2frame_b200/blind_denoising.py) from/to pinned host frames; "
+                       "(steps+1)/steps frames uploaded per step (the first frame of the run is only a `prev`)",
                 "psnr_db_last_frame": float(quality)},
         "gpu_launches": int(launches),
         "clocks": clocks,
@@ -202,7 +211,12 @@ def ours(args, rank, world, local_rank, ClockSampler, peaks):
                      "share_of_step": conv_ms / ms if ms else None,
                      "wgrad64": {"achieved": wg_tf, "frac": wg_tf / peak_tf if wg_tf else None,
                                  "avg_launch_us": wg_ms * 1e3 / wg_n if wg_n else None, "share_of_step": wg_ms / ms if ms else None},
-                     "traffic": None},
+                     # dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full (profiles/r01_ncu_conv64_wgrad64.txt):
+                     # forward k_conv64t<1,1> 266 + 218 MB, input gradient k_conv64t<0,2> 531 + 235 MB (algorithmic 531 / 796 MB;
+                     # the writes still dirty in the 126 MB L2 at kernel end are not counted by ncu); mean over the 15 + 15 launches
+                     "traffic": 625e6,
+                     "traffic_note": "mean of forward (484 MB) and input-gradient (766 MB) launches, ncu --set full, "
+                                     "profiles/r01_ncu_conv64_wgrad64.txt; wgrad64 1041 MB (algorithmic 1061 MB)"},
     }
     if world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline()

@@ -115,6 +115,38 @@ class OnlineF2F:
         self.finetune(curr, prev, flow, iters, losses)
         return self.denoise(curr)
 
+    def flows_ahead(self, frames, flow_kw=None):
+        """Backward flows of consecutive frames in ONE batched TV-L1 call: frames = [f_0 .. f_L] ([1,1,H,W] in
+        [0,1], on the device) -> flow[L,2,H,W], flow[k] from f_{k+1} to f_k (I0 = f_{k+1}, I1 = f_k on 0..255
+        values, tvl1flow.sh:11-14).  Frame pairs are independent (the reference runs one tvl1flow process per pair
+        over the whole sequence before denoising starts), so they advance in lock-step as slots of one launch
+        sequence instead of 2 300 latency-bound launches per pair."""
+        seq = torch.cat([f.to(self.dev, torch.float32).reshape(1, f.shape[-2], f.shape[-1]) for f in frames]) * 255.0
+        return tvl1flow(seq[1:], seq[:-1], **(flow_kw or {}))
+
+    def run_sequence(self, frames, iters=20, lookahead=16, flows=None, flow_kw=None, out=None, losses=None):
+        """The frame loop of blind_denoising.py:187-256 over frames[0..n-1] (host or device tensors [1,1,H,W]):
+        yields (i, denoised frame i) for i = 1..n-1.  flows: optional sequence with flows[i] = flow from frame i to
+        i-1 ([1,2,H,W]); when None they are computed on the device `lookahead` pairs at a time (flows_ahead).
+        out: optional pinned host tensors to receive the denoised frames (asynchronous D2H on the current stream)."""
+        n = len(frames)
+        i = 1
+        prev = frames[0].to(self.dev, non_blocking=True)
+        while i < n:
+            L = min(max(1, lookahead), n - i)
+            window = [prev] + [frames[k].to(self.dev, non_blocking=True) for k in range(i, i + L)]
+            wflows = None if flows is not None else self.flows_ahead(window, flow_kw)
+            for k in range(L):
+                curr = window[k + 1]
+                flow = flows[i + k] if flows is not None else wflows[k][None]
+                self.finetune(curr, window[k], flow, iters, losses)
+                den = self.denoise(curr)
+                if out is not None:
+                    out[i + k].copy_(den, non_blocking=True)
+                yield i + k, den
+            prev = window[L]
+            i += L
+
 
 # ------------------------------------------------------------------ file handling
 def _is_tiff(path):
@@ -159,15 +191,25 @@ def blind_denoising(**args):
     model = load_network(model_fn, dev)
     engine = OnlineF2F(model, align_corners=bool(args.get("align_corners", False)))
 
-    prev = torch.Tensor(_to_batch(imread_gray(args["input"] % (args["first"])))).to(dev)
+    first, last = args["first"], args["last"]
+
+    class _Frames:                       # frame k of the run = file index first + k, read when the loop reaches it
+        def __len__(self):
+            return last - first + 1
+
+        def __getitem__(self, k):
+            return torch.FloatTensor(_to_batch(imread_gray(args["input"] % (first + k))))
+
+    class _Flows:                        # --flow files: flow from frame i to frame i-1 (blind_denoising.py:206-209)
+        def __getitem__(self, k):
+            return torch.Tensor(np.expand_dims(read_flo(args["flow"] % (first + k)), 0)).permute(0, 3, 1, 2)
+
     plot_psnr = open(args["output_psnr"], "w")
-    for i in range(args["first"] + 1, args["last"] + 1):
+    flows = _Flows() if args.get("flow") else None
+    for k, den in engine.run_sequence(_Frames(), iters=args["iter"], lookahead=int(args.get("lookahead", 16) or 1),
+                                      flows=flows):
+        i = first + k
         print(i)
-        curr = torch.FloatTensor(_to_batch(imread_gray(args["input"] % (i)))).to(dev)
-        flow = None
-        if args.get("flow"):
-            flow = torch.Tensor(np.expand_dims(read_flo(args["flow"] % (i)), 0)).permute(0, 3, 1, 2)
-        den = engine.step_frame(curr, prev, flow, iters=args["iter"])
         den_np = np.array(den.cpu())
         if _is_tiff(args["ref"]):
             imsave(args["output"] % (i), np.squeeze(255. * den_np).astype(np.float32))
@@ -177,7 +219,6 @@ def blind_denoising(**args):
         quant = psnr(ref, den_np)
         plot_psnr.write(str(quant) + "\n")
         print(quant)
-        prev = curr
     torch.save([model, engine.optimizer], args["output_network"])
     plot_psnr.close()
 
@@ -196,6 +237,7 @@ def main(argv=None):
     parser.add_argument("--network", type=str, default="dncnn/logs/DnCNN-S-25/net.pth", help="path to the network")
     parser.add_argument("--gpu", type=int, default=0, help="(added) CUDA device index")
     parser.add_argument("--align_corners", action="store_true", help="(added) sample with align_corners=True")
+    parser.add_argument("--lookahead", type=int, default=16, help="(added) frame pairs per batched TV-L1 call when --flow is empty")
     argspar = parser.parse_args(argv)
     print("\n### Model-blind Video Denoising Via Frame-to-frame Training ###")
     print("> Parameters:")

@@ -678,6 +678,11 @@ k_conv64t(ConvArgs a, const __grid_constant__ CUtensorMap tm_in, const __grid_co
         const uint32_t a_lo0 = (uint32_t)ad0, a_hi = (uint32_t)(ad0 >> 32);
         const bool tr = a.trace != nullptr && el;
         long long tr_te = 0, tr_full = 0, tr_issue = 0;
+        // SM cycles against wall time over the tile loop of CTA 0: the clock the kernel actually ran at
+        // (back-to-back tensor kernels run under the power cap, an isolated launch does not)
+        const long long tr_c0 = tr ? clock64() : 0;
+        unsigned long long tr_g0 = 0;
+        if (tr) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tr_g0));
         int it = 0;
         for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it++) {
             const int s = it % NA, b = it & 1;
@@ -709,6 +714,12 @@ k_conv64t(ConvArgs a, const __grid_constant__ CUtensorMap tm_in, const __grid_co
         if (tr) {
             atomicAdd(a.trace + 2, (unsigned long long)tr_te); atomicAdd(a.trace + 3, (unsigned long long)tr_full);
             atomicAdd(a.trace + 4, (unsigned long long)tr_issue); atomicAdd(a.trace + 8, (unsigned long long)it);
+            if (blockIdx.x == 0) {
+                unsigned long long g1;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g1));
+                atomicAdd(a.trace + 10, (unsigned long long)(clock64() - tr_c0));
+                atomicAdd(a.trace + 11, g1 - tr_g0);
+            }
         }
     } else {
         // ===== epilogue: warps 0-3 take even tiles (accumulator 0), warps 4-7 odd tiles (accumulator 1) =====
@@ -755,12 +766,21 @@ k_conv64t(ConvArgs a, const __grid_constant__ CUtensorMap tm_in, const __grid_co
                 acc1[j] += __shfl_xor_sync(0xffffffffu, acc1[j], 8);
                 acc1[j] += __shfl_xor_sync(0xffffffffu, acc1[j], 16);
             }
+            // The eight epilogue warps' sums are combined in shared memory first and the CTA issues ONE atomic per
+            // value: FP64 atomics on the same 128 addresses serialise in L2 (measured: 8 x 148 atomics per address
+            // cost 25-35 us at the end of every launch, profiles/r01_conv64_role_trace_clock.log).
+            float *red = reinterpret_cast<float *>(stg);          // this warp's staging area, free after its last tile
             if (lane < 8) {
 #pragma unroll
-                for (int j = 0; j < 8; j++) {
-                    atomicAdd(a.stats + lane * 8 + j, (double)acc0[j]);
-                    atomicAdd(a.stats + 64 + lane * 8 + j, (double)acc1[j]);
-                }
+                for (int j = 0; j < 8; j++) { red[lane * 8 + j] = acc0[j]; red[64 + lane * 8 + j] = acc1[j]; }
+            }
+            asm volatile("bar.sync 1, 256;" ::: "memory");        // the 8 epilogue warps only
+            if (threadIdx.x < 128) {
+                double t = 0.0;
+#pragma unroll
+                for (int w = 0; w < NEPI; w++)
+                    t += (double)reinterpret_cast<const float *>(smem + OFF_EPI + w * EPI_WARP)[threadIdx.x];
+                atomicAdd(a.stats + threadIdx.x, t);
             }
         }
     }

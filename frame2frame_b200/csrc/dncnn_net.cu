@@ -65,24 +65,37 @@ __global__ void __launch_bounds__(256) k_conv_first(const float *__restrict__ x,
 #pragma unroll
         for (int j = 0; j < 8; j++) w[t][j] = w0[(chunk * 8 + j) * 9 + t];
     const size_t P = (size_t)H * W;
-    for (size_t p = (size_t)blockIdx.x * 32 + (threadIdx.x >> 3); p < P; p += (size_t)gridDim.x * 32) {
-        const int y = (int)(p / W), xx = (int)(p % W);
-        float acc[8];
+    constexpr int NP = 2;       // two pixels per thread and iteration, their 18 loads in flight together
+    for (size_t p0 = (size_t)blockIdx.x * (32 * NP) + (threadIdx.x >> 3); p0 < P; p0 += (size_t)gridDim.x * (32 * NP)) {
+        float xv[NP][9];
 #pragma unroll
-        for (int j = 0; j < 8; j++) acc[j] = 0.0f;
+        for (int u = 0; u < NP; u++) {
+            const size_t p = p0 + 32 * u;
+            const int y = (int)(p / W), xx = (int)(p % W);
 #pragma unroll
-        for (int t = 0; t < 9; t++) {
-            const int yy = y + t / 3 - 1, xq = xx + t % 3 - 1;
-            const float v = (yy >= 0 && yy < H && xq >= 0 && xq < W) ? __ldg(x + (size_t)yy * W + xq) : 0.0f;
-#pragma unroll
-            for (int j = 0; j < 8; j++) acc[j] = fmaf(v, w[t][j], acc[j]);
+            for (int t = 0; t < 9; t++) {
+                const int yy = y + t / 3 - 1, xq = xx + t % 3 - 1;
+                xv[u][t] = (p < P && yy >= 0 && yy < H && xq >= 0 && xq < W) ? __ldg(x + (size_t)yy * W + xq) : 0.0f;
+            }
         }
-        uint4 o;
-        o.x = pack_bf16(fmaxf(acc[0], 0.f), fmaxf(acc[1], 0.f));
-        o.y = pack_bf16(fmaxf(acc[2], 0.f), fmaxf(acc[3], 0.f));
-        o.z = pack_bf16(fmaxf(acc[4], 0.f), fmaxf(acc[5], 0.f));
-        o.w = pack_bf16(fmaxf(acc[6], 0.f), fmaxf(acc[7], 0.f));
-        *reinterpret_cast<uint4 *>(a0 + p * 64 + chunk * 8) = o;
+#pragma unroll
+        for (int u = 0; u < NP; u++) {
+            const size_t p = p0 + 32 * u;
+            if (p >= P) continue;
+            float acc[8];
+#pragma unroll
+            for (int j = 0; j < 8; j++) acc[j] = 0.0f;
+#pragma unroll
+            for (int t = 0; t < 9; t++)
+#pragma unroll
+                for (int j = 0; j < 8; j++) acc[j] = fmaf(xv[u][t], w[t][j], acc[j]);
+            uint4 o;
+            o.x = pack_bf16(fmaxf(acc[0], 0.f), fmaxf(acc[1], 0.f));
+            o.y = pack_bf16(fmaxf(acc[2], 0.f), fmaxf(acc[3], 0.f));
+            o.z = pack_bf16(fmaxf(acc[4], 0.f), fmaxf(acc[5], 0.f));
+            o.w = pack_bf16(fmaxf(acc[6], 0.f), fmaxf(acc[7], 0.f));
+            *reinterpret_cast<uint4 *>(a0 + p * 64 + chunk * 8) = o;
+        }
     }
 }
 
@@ -176,31 +189,48 @@ __device__ __forceinline__ void block_chunk_reduce(float (&v)[NV], float *red /*
 // products of that pixel, the output pixel then sums nine shifted partials from shared memory.
 // out = n (the noise estimate, SaoYan's forward) or x - n (net.py:31) when `residual`.
 constexpr int LT = 16, LH = LT + 2, LHP = LH * LH;
+constexpr int LBW_STRIDE = 76;     // floats between the per-chunk weight tables in shared memory (conflict-free 16-byte reads)
 __global__ void __launch_bounds__(256) k_conv_last(const bf16 *__restrict__ z, const float *__restrict__ coef,
                                                    const float *__restrict__ w16, const float *__restrict__ x,
                                                    float *__restrict__ out, int H, int W, int tiles_x, int ntiles,
                                                    int residual)
 {
     __shared__ float T[LHP * 9 + 4];
+    __shared__ __align__(16) float wS[8 * LBW_STRIDE];   // [chunk][tap][8 channels]: registers go to the loads in flight
     const int chunk = threadIdx.x & 7;
-    float w[9][8], sc[8], sh[8];
-#pragma unroll
-    for (int t = 0; t < 9; t++)
-#pragma unroll
-        for (int j = 0; j < 8; j++) w[t][j] = w16[(chunk * 8 + j) * 9 + t];
+    for (int e = threadIdx.x; e < 8 * 72; e += 256) {
+        const int c = e / 72, t = (e % 72) >> 3, j = e & 7;
+        wS[c * LBW_STRIDE + t * 8 + j] = w16[(c * 8 + j) * 9 + t];
+    }
+    float sc[8], sh[8];
 #pragma unroll
     for (int j = 0; j < 8; j++) { sc[j] = coef[C_SCALE + chunk * 8 + j]; sh[j] = coef[C_SHIFT + chunk * 8 + j]; }
+    __syncthreads();
+    const float4 *wv = reinterpret_cast<const float4 *>(wS + chunk * LBW_STRIDE);
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         const int ty0 = (tile / tiles_x) * LT, tx0 = (tile % tiles_x) * LT;
-        for (int task = threadIdx.x; task < LHP * 8; task += 256) {
-            const int pix = task >> 3;
+        // the whole haloed tile's loads are issued before any arithmetic (one exposed memory latency per tile, not eleven)
+        constexpr int ROUNDS = (LHP * 8 + 255) / 256;
+        uint4 v[ROUNDS];
+        uint32_t okm = 0;
+#pragma unroll
+        for (int r = 0; r < ROUNDS; r++) {
+            const int pix = (threadIdx.x + 256 * r) >> 3;
             const int gy = ty0 - 1 + pix / LH, gx = tx0 - 1 + pix % LH;
+            v[r] = make_uint4(0, 0, 0, 0);
+            if (pix < LHP && gy >= 0 && gy < H && gx >= 0 && gx < W) {
+                okm |= 1u << r;
+                v[r] = __ldg(reinterpret_cast<const uint4 *>(z + ((size_t)gy * W + gx) * 64 + chunk * 8));
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < ROUNDS; r++) {
+            const int pix = (threadIdx.x + 256 * r) >> 3;
             float part[9];
 #pragma unroll
             for (int t = 0; t < 9; t++) part[t] = 0.0f;
-            if (gy >= 0 && gy < H && gx >= 0 && gx < W) {
-                const uint4 v = __ldg(reinterpret_cast<const uint4 *>(z + ((size_t)gy * W + gx) * 64 + chunk * 8));
-                const uint32_t vw[4] = {v.x, v.y, v.z, v.w};
+            if ((okm >> r) & 1u) {
+                const uint32_t vw[4] = {v[r].x, v[r].y, v[r].z, v[r].w};
                 float a[8];
 #pragma unroll
                 for (int q = 0; q < 4; q++) {
@@ -209,10 +239,13 @@ __global__ void __launch_bounds__(256) k_conv_last(const bf16 *__restrict__ z, c
                     a[2 * q + 1] = fmaxf(fmaf(f.y, sc[2 * q + 1], sh[2 * q + 1]), 0.0f);
                 }
 #pragma unroll
-                for (int t = 0; t < 9; t++)
-#pragma unroll
-                    for (int j = 0; j < 8; j++) part[t] = fmaf(a[j], w[t][j], part[t]);
+                for (int t = 0; t < 9; t++) {
+                    const float4 w0 = wv[2 * t], w1 = wv[2 * t + 1];
+                    part[t] = fmaf(a[0], w0.x, fmaf(a[1], w0.y, fmaf(a[2], w0.z, fmaf(a[3], w0.w, 0.0f)))) +
+                              fmaf(a[4], w1.x, fmaf(a[5], w1.y, fmaf(a[6], w1.z, fmaf(a[7], w1.w, 0.0f))));
+                }
             }
+            // every lane takes part in the shuffles (groups of 8 lanes share a pixel); only the store is guarded
 #pragma unroll
             for (int t = 0; t < 9; t++) {
                 part[t] += __shfl_xor_sync(0xffffffffu, part[t], 1);
@@ -223,8 +256,10 @@ __global__ void __launch_bounds__(256) k_conv_last(const bf16 *__restrict__ z, c
             float mine = part[0];
 #pragma unroll
             for (int t = 1; t < 8; t++) mine = (chunk == t) ? part[t] : mine;
-            T[pix * 9 + chunk] = mine;
-            if (chunk == 0) T[pix * 9 + 8] = part[8];
+            if (pix < LHP) {
+                T[pix * 9 + chunk] = mine;
+                if (chunk == 0) T[pix * 9 + 8] = part[8];
+            }
         }
         __syncthreads();
         {
@@ -246,6 +281,7 @@ __global__ void __launch_bounds__(256) k_conv_last(const bf16 *__restrict__ z, c
 // its BatchNorm-backward sums, and the last layer's weight gradient -- one pass over z15.
 //   g15[q][ic]      = relu'(.) * sum_k dn[q - k + 1] * w16[ic][k]
 //   dW16[ic][k]     = sum_q a15[q][ic] * dn[q - k + 1]
+constexpr int LBW_SMEM = 64 * 88 * 4 + 8 * LBW_STRIDE * 4;
 __global__ void __launch_bounds__(256, 1) k_conv_last_bwd(const float *__restrict__ dy, float dy_sign,
                                                           const bf16 *__restrict__ z, const float *__restrict__ coef,
                                                           const float *__restrict__ w16, bf16 *__restrict__ g,
@@ -253,60 +289,82 @@ __global__ void __launch_bounds__(256, 1) k_conv_last_bwd(const float *__restric
                                                           int W)
 {
     extern __shared__ float red[];
+    float *wS = red + 64 * 88;                   // [chunk][tap][8 channels]
     const int chunk = threadIdx.x & 7;
-    float w[9][8], sc[8], sh[8], mu[8], is[8];
-#pragma unroll
-    for (int t = 0; t < 9; t++)
-#pragma unroll
-        for (int j = 0; j < 8; j++) w[t][j] = w16[(chunk * 8 + j) * 9 + t];
+    for (int e = threadIdx.x; e < 8 * 72; e += 256) {
+        const int c = e / 72, t = (e % 72) >> 3, j = e & 7;
+        wS[c * LBW_STRIDE + t * 8 + j] = w16[(c * 8 + j) * 9 + t];
+    }
+    float sc[8], sh[8], mu[8], is[8];
 #pragma unroll
     for (int j = 0; j < 8; j++) {
         sc[j] = coef[C_SCALE + chunk * 8 + j]; sh[j] = coef[C_SHIFT + chunk * 8 + j];
         mu[j] = coef[C_MEAN + chunk * 8 + j]; is[j] = coef[C_INVSTD + chunk * 8 + j];
     }
+    __syncthreads();
+    const float4 *wv = reinterpret_cast<const float4 *>(wS + chunk * LBW_STRIDE);
     float acc[88];   // [0,72): dW16[tap][j]; [72,80): sum g; [80,88): sum g*xhat
 #pragma unroll
     for (int i = 0; i < 88; i++) acc[i] = 0.0f;
     const size_t P = (size_t)H * W;
-    for (size_t p = (size_t)blockIdx.x * 32 + (threadIdx.x >> 3); p < P; p += (size_t)gridDim.x * 32) {
-        const int y = (int)(p / W), xx = (int)(p % W);
-        float dn[9];
+    // Two pixels per thread and iteration, all their loads issued before any arithmetic: with 8 warps per SM
+    // (the 88 accumulators bound the occupancy) the loop is otherwise one exposed DRAM latency per pixel.
+    constexpr int NP = 2;
+    for (size_t p0 = (size_t)blockIdx.x * (32 * NP) + (threadIdx.x >> 3); p0 < P; p0 += (size_t)gridDim.x * (32 * NP)) {
+        uint4 v[NP];
+        float dn[NP][9];
+        bool ok[NP];
 #pragma unroll
-        for (int t = 0; t < 9; t++) {
-            const int yy = y - (t / 3) + 1, xq = xx - (t % 3) + 1;
-            dn[t] = (yy >= 0 && yy < H && xq >= 0 && xq < W) ? dy_sign * __ldg(dy + (size_t)yy * W + xq) : 0.0f;
-        }
-        const uint4 v = __ldg(reinterpret_cast<const uint4 *>(z + p * 64 + chunk * 8));
-        const uint32_t vw[4] = {v.x, v.y, v.z, v.w};
-        float zz[8];
-#pragma unroll
-        for (int q = 0; q < 4; q++) { const float2 f = unpack_bf16(vw[q]); zz[2 * q] = f.x; zz[2 * q + 1] = f.y; }
-        float gg[8];
-#pragma unroll
-        for (int j = 0; j < 8; j++) {
-            const float yv = fmaf(zz[j], sc[j], sh[j]);
-            const float a = fmaxf(yv, 0.0f);
-            float s = 0.0f;
+        for (int u = 0; u < NP; u++) {
+            const size_t p = p0 + 32 * u;
+            ok[u] = p < P;
+            v[u] = make_uint4(0, 0, 0, 0);
+            if (ok[u]) v[u] = __ldg(reinterpret_cast<const uint4 *>(z + p * 64 + chunk * 8));
+            const int y = (int)(p / W), xx = (int)(p % W);
 #pragma unroll
             for (int t = 0; t < 9; t++) {
-                s = fmaf(dn[t], w[t][j], s);
-                acc[t * 8 + j] = fmaf(a, dn[t], acc[t * 8 + j]);
+                const int yy = y - (t / 3) + 1, xq = xx - (t % 3) + 1;
+                dn[u][t] = (ok[u] && yy >= 0 && yy < H && xq >= 0 && xq < W) ? dy_sign * __ldg(dy + (size_t)yy * W + xq) : 0.0f;
             }
-            gg[j] = yv > 0.0f ? s : 0.0f;
         }
-        uint4 o;
-        o.x = pack_bf16(gg[0], gg[1]); o.y = pack_bf16(gg[2], gg[3]);
-        o.z = pack_bf16(gg[4], gg[5]); o.w = pack_bf16(gg[6], gg[7]);
-        *reinterpret_cast<uint4 *>(g + p * 64 + chunk * 8) = o;
-        const uint32_t ow[4] = {o.x, o.y, o.z, o.w};
 #pragma unroll
-        for (int q = 0; q < 4; q++) {                  // sums of the ROUNDED gradient, like the tcgen05 epilogue
-            const float2 f = unpack_bf16(ow[q]);
-            acc[72 + 2 * q] += f.x; acc[72 + 2 * q + 1] += f.y;
-            acc[80 + 2 * q] = fmaf(f.x, (zz[2 * q] - mu[2 * q]) * is[2 * q], acc[80 + 2 * q]);
-            acc[80 + 2 * q + 1] = fmaf(f.y, (zz[2 * q + 1] - mu[2 * q + 1]) * is[2 * q + 1], acc[80 + 2 * q + 1]);
+        for (int u = 0; u < NP; u++) {
+            if (!ok[u]) continue;
+            const size_t p = p0 + 32 * u;
+            const uint32_t vw[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+            float zz[8], a[8], s[8];
+#pragma unroll
+            for (int q = 0; q < 4; q++) { const float2 f = unpack_bf16(vw[q]); zz[2 * q] = f.x; zz[2 * q + 1] = f.y; }
+#pragma unroll
+            for (int j = 0; j < 8; j++) { a[j] = fmaf(zz[j], sc[j], sh[j]); s[j] = 0.0f; }   // a = pre-ReLU BN output for now
+#pragma unroll
+            for (int t = 0; t < 9; t++) {
+                const float4 w0 = wv[2 * t], w1 = wv[2 * t + 1];
+                const float wt[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    s[j] = fmaf(dn[u][t], wt[j], s[j]);
+                    acc[t * 8 + j] = fmaf(fmaxf(a[j], 0.0f), dn[u][t], acc[t * 8 + j]);
+                }
+            }
+            float gg[8];
+#pragma unroll
+            for (int j = 0; j < 8; j++) gg[j] = a[j] > 0.0f ? s[j] : 0.0f;
+            uint4 o;
+            o.x = pack_bf16(gg[0], gg[1]); o.y = pack_bf16(gg[2], gg[3]);
+            o.z = pack_bf16(gg[4], gg[5]); o.w = pack_bf16(gg[6], gg[7]);
+            *reinterpret_cast<uint4 *>(g + p * 64 + chunk * 8) = o;
+            const uint32_t ow[4] = {o.x, o.y, o.z, o.w};
+#pragma unroll
+            for (int q = 0; q < 4; q++) {                  // sums of the ROUNDED gradient, like the tcgen05 epilogue
+                const float2 f = unpack_bf16(ow[q]);
+                acc[72 + 2 * q] += f.x; acc[72 + 2 * q + 1] += f.y;
+                acc[80 + 2 * q] = fmaf(f.x, (zz[2 * q] - mu[2 * q]) * is[2 * q], acc[80 + 2 * q]);
+                acc[80 + 2 * q + 1] = fmaf(f.y, (zz[2 * q + 1] - mu[2 * q + 1]) * is[2 * q + 1], acc[80 + 2 * q + 1]);
+            }
         }
     }
+    __syncthreads();
     block_chunk_reduce<88>(acc, red, [&](int ch, int i) -> double * {
         if (i < 72) return dw16 + (ch * 8 + (i & 7)) * 9 + (i >> 3);
         if (i < 80) return stats + ch * 8 + (i - 72);
@@ -324,23 +382,33 @@ __global__ void __launch_bounds__(256, 1) k_wgrad_first(const bf16 *__restrict__
 #pragma unroll
     for (int i = 0; i < 72; i++) acc[i] = 0.0f;
     const size_t P = (size_t)H * W;
-    for (size_t p = (size_t)blockIdx.x * 32 + (threadIdx.x >> 3); p < P; p += (size_t)gridDim.x * 32) {
-        const int y = (int)(p / W), xx = (int)(p % W);
-        float xv[9];
+    constexpr int NP = 2;       // two pixels per thread and iteration, all their loads in flight together
+    for (size_t p0 = (size_t)blockIdx.x * (32 * NP) + (threadIdx.x >> 3); p0 < P; p0 += (size_t)gridDim.x * (32 * NP)) {
+        float xv[NP][9];
+        uint4 v[NP];
 #pragma unroll
-        for (int t = 0; t < 9; t++) {
-            const int yy = y + t / 3 - 1, xq = xx + t % 3 - 1;
-            xv[t] = (yy >= 0 && yy < H && xq >= 0 && xq < W) ? __ldg(x + (size_t)yy * W + xq) : 0.0f;
-        }
-        const uint4 v = __ldg(reinterpret_cast<const uint4 *>(g0 + p * 64 + chunk * 8));
-        const uint32_t vw[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-        for (int q = 0; q < 4; q++) {
-            const float2 f = unpack_bf16(vw[q]);
+        for (int u = 0; u < NP; u++) {
+            const size_t p = p0 + 32 * u;
+            const int y = (int)(p / W), xx = (int)(p % W);
+            v[u] = make_uint4(0, 0, 0, 0);          // a zero gradient adds nothing: out-of-range pixels need no branch below
+            if (p < P) v[u] = __ldg(reinterpret_cast<const uint4 *>(g0 + p * 64 + chunk * 8));
 #pragma unroll
             for (int t = 0; t < 9; t++) {
-                acc[t * 8 + 2 * q] = fmaf(f.x, xv[t], acc[t * 8 + 2 * q]);
-                acc[t * 8 + 2 * q + 1] = fmaf(f.y, xv[t], acc[t * 8 + 2 * q + 1]);
+                const int yy = y + t / 3 - 1, xq = xx + t % 3 - 1;
+                xv[u][t] = (p < P && yy >= 0 && yy < H && xq >= 0 && xq < W) ? __ldg(x + (size_t)yy * W + xq) : 0.0f;
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < NP; u++) {
+            const uint32_t vw[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                const float2 f = unpack_bf16(vw[q]);
+#pragma unroll
+                for (int t = 0; t < 9; t++) {
+                    acc[t * 8 + 2 * q] = fmaf(f.x, xv[u][t], acc[t * 8 + 2 * q]);
+                    acc[t * 8 + 2 * q + 1] = fmaf(f.y, xv[u][t], acc[t * 8 + 2 * q + 1]);
+                }
             }
         }
     }
@@ -396,20 +464,29 @@ __global__ void k_adam(float *__restrict__ p, const float *__restrict__ g, float
 // k_bn_bwd_coeffs) from the ReLU-masked gradient g and the pre-BN output z of the layer, and is
 // also written back over g so that the input-gradient convolution that follows reads dz directly.
 namespace wg {
+// Tile = TR output rows x 16 pixels.  The producers are latency-bound (one DRAM round trip per tile and warp:
+// ncu shows 47 % of the samples on the first use of the loaded registers), so the pipeline is made deep rather than
+// wide: small tiles, FOUR stages, and TWO producer groups that fill alternate tiles -- every group has two tiles of
+// slack before the MMA warp catches up with it.
+constexpr int TR = 8;                   // output rows per tile
+constexpr int HR = TR + 2;              // halo rows
 constexpr int A_S = 19 * 16;            // 304 B between chunk lines (18 pixels + 1 pad: conflict-free 16-byte stores)
 constexpr int A_R = 8 * A_S;            // 2432 B between halo rows
-constexpr int A_ROWS = 19;              // 18 halo rows + the row the (r+2, r+3) pair touches beyond them
-constexpr int A_BYTES = A_ROWS * A_R;   // 46208
+constexpr int A_ROWS = HR + 1;          // halo rows + the row the (r+2, r+3) pair touches beyond them
+constexpr int A_BYTES = A_ROWS * A_R;
 constexpr int D_S = 17 * 16;            // 272
 constexpr int D_R = 8 * D_S;            // 2176
-constexpr int D_BYTES = 16 * D_R;       // 34816
-constexpr int STAGE = A_BYTES + D_BYTES;
-constexpr int STAGES = 2;
+constexpr int D_BYTES = TR * D_R;
+constexpr int STAGE = A_BYTES + D_BYTES;     // 44 160 B
+constexpr int STAGES = 4;
+constexpr int NGROUPS = 2;              // producer groups (tile it is staged by group it % NGROUPS into stage it % STAGES)
 constexpr int OFF_BAR = STAGES * STAGE;
 constexpr int SMEM_BYTES = OFF_BAR + 128;
-constexpr int NTHREADS = 288;
+constexpr int MMA_WARP = 8;
+constexpr int NTHREADS = (9 + 8 * (NGROUPS - 1)) * 32;   // group 0: warps 0-7, MMA: warp 8, group 1: warps 9-16
 constexpr int TMEM_COLS = 512;
 constexpr int PARTIAL = 6 * 128 * 64;   // floats per CTA
+constexpr int HPIX = HR * 18, DPIX = TR * 16;
 
 struct Args {
     const bf16 *act;       // layer input: z_{k-1} (BN+ReLU applied on load) or a_0 (raw)
@@ -428,19 +505,19 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a)
     const int ntiles = a.tiles_x * a.tiles_y;
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + OFF_BAR);
     const uint32_t bar0 = smem_u32(bars);
-    auto BAR = [&](int i) { return bar0 + 8u * i; };   // full[2] @0, empty[2] @2, done @4; tmem ptr @ +8
-    uint32_t *tmem_ptr = reinterpret_cast<uint32_t *>(bars + 8);
+    auto BAR = [&](int i) { return bar0 + 8u * i; };   // full[STAGES] @0, empty[STAGES] @STAGES, done @2*STAGES; tmem ptr after
+    uint32_t *tmem_ptr = reinterpret_cast<uint32_t *>(bars + 2 * STAGES + 2);
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < STAGES; s++) { mbar_init(BAR(s), 256); mbar_init(BAR(2 + s), 1); }
-        mbar_init(BAR(4), 1);
+        for (int s = 0; s < STAGES; s++) { mbar_init(BAR(s), 256); mbar_init(BAR(STAGES + s), 1); }
+        mbar_init(BAR(2 * STAGES), 1);
         mbar_fence_init();
     }
-    if (warp == 8) tmem_alloc(smem_u32(tmem_ptr), TMEM_COLS);
+    if (warp == MMA_WARP) tmem_alloc(smem_u32(tmem_ptr), TMEM_COLS);
     // the extra halo row of each stage is only ever multiplied into unused accumulator rows; keep it finite
     for (int i = threadIdx.x; i < STAGES * (A_R / 16); i += NTHREADS) {
         const int s = i / (A_R / 16), o = i % (A_R / 16);
-        *reinterpret_cast<uint4 *>(smem + s * STAGE + 18 * A_R + o * 16) = make_uint4(0, 0, 0, 0);
+        *reinterpret_cast<uint4 *>(smem + s * STAGE + HR * A_R + o * 16) = make_uint4(0, 0, 0, 0);
     }
     fence_proxy_async();
     fence_before_sync();
@@ -448,9 +525,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a)
     fence_after_sync();
     const uint32_t tmem_base = *tmem_ptr;
 
-    if (warp < 4) {
-        // ===== producer of the activation tile (18x18 halo) =====
-        const int ptid = threadIdx.x, chunk = ptid & 7;
+    // role of this warp: producer warp index pw in 0..7 of group grp, or the MMA warp
+    const int grp = warp > MMA_WARP ? 1 : 0;
+    const int pw = warp > MMA_WARP ? warp - (MMA_WARP + 1) : warp;
+
+    if (warp != MMA_WARP && pw < 4) {
+        // ===== producer of the activation tile (HR x 18 halo) =====
+        const int ptid = pw * 32 + lane, chunk = ptid & 7;
         float sc[8], sh[8];
 #pragma unroll
         for (int j = 0; j < 8; j++) {
@@ -458,121 +539,120 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a)
             sh[j] = a.coef_in ? a.coef_in[C_SHIFT + chunk * 8 + j] : 0.0f;
         }
         const bool bn = a.coef_in != nullptr;
-        int it = 0;
-        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it++) {
-            const int s = it & 1;
-            mbar_wait(BAR(2 + s), ((it >> 1) & 1) ^ 1);
+        int it = grp;
+        for (int tile = blockIdx.x + grp * gridDim.x; tile < ntiles; tile += NGROUPS * gridDim.x, it += NGROUPS) {
+            const int s = it % STAGES;
+            mbar_wait(BAR(STAGES + s), ((it / STAGES) & 1) ^ 1);
             uint8_t *dstA = smem + s * STAGE;
-            const int ty0 = (tile / a.tiles_x) * 16 - 1, tx0 = (tile % a.tiles_x) * 16 - 1;
-            constexpr int ROUNDS = (324 + 15) / 16, U = ROUNDS;   // the whole tile's loads in flight at once (latency-bound otherwise)
-            int pix = ptid >> 3;
-#pragma unroll 1
-            for (int r0 = 0; r0 < ROUNDS; r0 += U) {
-                uint4 v[U];
-                bool inb[U];
-                int px[U];
+            const int ty0 = (tile / a.tiles_x) * TR - 1, tx0 = (tile % a.tiles_x) * 16 - 1;
+            constexpr int U = (HPIX + 15) / 16;   // the whole tile's loads in flight at once
+            uint4 v[U];
+            uint32_t inb = 0;
 #pragma unroll
-                for (int u = 0; u < U; u++) {
-                    px[u] = pix;
-                    const int gy = ty0 + pix / 18, gx = tx0 + pix % 18;
-                    inb[u] = pix < 324 && gy >= 0 && gy < a.H && gx >= 0 && gx < a.W;
-                    v[u] = make_uint4(0, 0, 0, 0);
-                    if (inb[u]) v[u] = __ldg(reinterpret_cast<const uint4 *>(a.act + ((size_t)gy * a.W + gx) * 64 + chunk * 8));
-                    pix += 16;
+            for (int u = 0; u < U; u++) {
+                const int pix = (ptid >> 3) + 16 * u;
+                const int gy = ty0 + pix / 18, gx = tx0 + pix % 18;
+                v[u] = make_uint4(0, 0, 0, 0);
+                if (pix < HPIX && gy >= 0 && gy < a.H && gx >= 0 && gx < a.W) {
+                    inb |= 1u << u;
+                    v[u] = __ldg(reinterpret_cast<const uint4 *>(a.act + ((size_t)gy * a.W + gx) * 64 + chunk * 8));
                 }
+            }
 #pragma unroll
-                for (int u = 0; u < U; u++) {
-                    if (px[u] < 324) {
-                        uint4 o = v[u];
-                        if (bn && inb[u]) {
-                            uint32_t w[4] = {o.x, o.y, o.z, o.w};
+            for (int u = 0; u < U; u++) {
+                const int pix = (ptid >> 3) + 16 * u;
+                if (pix < HPIX) {
+                    uint4 o = v[u];
+                    if (bn && ((inb >> u) & 1u)) {
+                        uint32_t w[4] = {o.x, o.y, o.z, o.w};
 #pragma unroll
-                            for (int j = 0; j < 4; j++) {
-                                const float2 f = unpack_bf16(w[j]);
-                                w[j] = pack_bf16(fmaxf(fmaf(f.x, sc[2 * j], sh[2 * j]), 0.0f),
-                                                 fmaxf(fmaf(f.y, sc[2 * j + 1], sh[2 * j + 1]), 0.0f));
-                            }
-                            o = make_uint4(w[0], w[1], w[2], w[3]);
+                        for (int j = 0; j < 4; j++) {
+                            const float2 f = unpack_bf16(w[j]);
+                            w[j] = pack_bf16(fmaxf(fmaf(f.x, sc[2 * j], sh[2 * j]), 0.0f),
+                                             fmaxf(fmaf(f.y, sc[2 * j + 1], sh[2 * j + 1]), 0.0f));
                         }
-                        *reinterpret_cast<uint4 *>(dstA + (px[u] / 18) * A_R + chunk * A_S + (px[u] % 18) * 16) = o;
+                        o = make_uint4(w[0], w[1], w[2], w[3]);
                     }
+                    *reinterpret_cast<uint4 *>(dstA + (pix / 18) * A_R + chunk * A_S + (pix % 18) * 16) = o;
                 }
             }
             fence_proxy_async();
             mbar_arrive(BAR(s));
         }
-        // ===== after the last tile: accumulators -> this CTA's partial =====
-        mbar_wait(BAR(4), 0);
-        fence_after_sync();
-        float *dst = a.partial + (size_t)blockIdx.x * PARTIAL;
-        const int row = warp * 32 + lane;
+        if (grp == 0) {
+            // ===== after the last tile: accumulators -> this CTA's partial (warps 0-3 = the four TMEM lane quadrants) =====
+            mbar_wait(BAR(2 * STAGES), 0);
+            fence_after_sync();
+            float *dst = a.partial + (size_t)blockIdx.x * PARTIAL;
+            const int row = warp * 32 + lane;
 #pragma unroll 1
-        for (int j = 0; j < 6; j++) {
+            for (int j = 0; j < 6; j++) {
 #pragma unroll 1
-            for (int part = 0; part < 2; part++) {
-                uint32_t r[32];
-                tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + j * 64 + part * 32, r);
-                tmem_ld_wait();
-                if (j < 3 || row < 64) {
-                    float4 *o = reinterpret_cast<float4 *>(dst + ((size_t)j * 128 + row) * 64 + part * 32);
+                for (int part = 0; part < 2; part++) {
+                    uint32_t r[32];
+                    tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + j * 64 + part * 32, r);
+                    tmem_ld_wait();
+                    if (j < 3 || row < 64) {
+                        float4 *o = reinterpret_cast<float4 *>(dst + ((size_t)j * 128 + row) * 64 + part * 32);
 #pragma unroll
-                    for (int q = 0; q < 8; q++)
-                        o[q] = make_float4(__uint_as_float(r[4 * q]), __uint_as_float(r[4 * q + 1]),
-                                           __uint_as_float(r[4 * q + 2]), __uint_as_float(r[4 * q + 3]));
+                        for (int q = 0; q < 8; q++)
+                            o[q] = make_float4(__uint_as_float(r[4 * q]), __uint_as_float(r[4 * q + 1]),
+                                               __uint_as_float(r[4 * q + 2]), __uint_as_float(r[4 * q + 3]));
+                    }
                 }
             }
         }
-    } else if (warp < 8) {
-        // ===== producer of the dz tile (16x16, no halo); writes dz back over g =====
-        const int ptid = threadIdx.x - 128, chunk = ptid & 7;
+    } else if (warp != MMA_WARP) {
+        // ===== producer of the dz tile (TR x 16, no halo); writes dz back over g =====
+        const int ptid = (pw - 4) * 32 + lane, chunk = ptid & 7;
         float cA[8], cB[8], cC[8];
 #pragma unroll
         for (int j = 0; j < 8; j++) {
             cA[j] = a.coef[C_A + chunk * 8 + j]; cB[j] = a.coef[C_B + chunk * 8 + j]; cC[j] = a.coef[C_C + chunk * 8 + j];
         }
-        int it = 0;
-        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it++) {
-            const int s = it & 1;
-            mbar_wait(BAR(2 + s), ((it >> 1) & 1) ^ 1);
+        int it = grp;
+        for (int tile = blockIdx.x + grp * gridDim.x; tile < ntiles; tile += NGROUPS * gridDim.x, it += NGROUPS) {
+            const int s = it % STAGES;
+            mbar_wait(BAR(STAGES + s), ((it / STAGES) & 1) ^ 1);
             uint8_t *dstD = smem + s * STAGE + A_BYTES;
-            const int ty0 = (tile / a.tiles_x) * 16, tx0 = (tile % a.tiles_x) * 16;
-            constexpr int U = 8;
+            const int ty0 = (tile / a.tiles_x) * TR, tx0 = (tile % a.tiles_x) * 16;
+            constexpr int U = DPIX / 32;          // two passes of 4 rounds x 16 pixels (register budget: 17 warps -> 96 registers)
 #pragma unroll 1
-            for (int r0 = 0; r0 < 16; r0 += U) {
-                uint4 vg[U], vz[U];
-                bool inb[U];
+            for (int r0 = 0; r0 < DPIX / 16; r0 += U) {
+            uint4 vg[U], vz[U];
+            uint32_t inb = 0;
 #pragma unroll
-                for (int u = 0; u < U; u++) {
-                    const int pix = (ptid >> 3) + 16 * (r0 + u);
+            for (int u = 0; u < U; u++) {
+                const int pix = (ptid >> 3) + 16 * (r0 + u);
+                const int gy = ty0 + (pix >> 4), gx = tx0 + (pix & 15);
+                vg[u] = vz[u] = make_uint4(0, 0, 0, 0);
+                if (gy < a.H && gx < a.W) {
+                    inb |= 1u << u;
+                    const size_t o = ((size_t)gy * a.W + gx) * 64 + chunk * 8;
+                    vg[u] = *reinterpret_cast<const uint4 *>(a.g + o);
+                    vz[u] = __ldg(reinterpret_cast<const uint4 *>(a.z + o));
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                const int pix = (ptid >> 3) + 16 * (r0 + u);
+                uint4 o = make_uint4(0, 0, 0, 0);
+                if ((inb >> u) & 1u) {
+                    const uint32_t gw[4] = {vg[u].x, vg[u].y, vg[u].z, vg[u].w};
+                    const uint32_t zw[4] = {vz[u].x, vz[u].y, vz[u].z, vz[u].w};
+                    uint32_t w[4];
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        const float2 gg = unpack_bf16(gw[j]), zz = unpack_bf16(zw[j]);
+                        w[j] = pack_bf16(fmaf(cA[2 * j], gg.x, fmaf(cB[2 * j], zz.x, cC[2 * j])),
+                                         fmaf(cA[2 * j + 1], gg.y, fmaf(cB[2 * j + 1], zz.y, cC[2 * j + 1])));
+                    }
+                    o = make_uint4(w[0], w[1], w[2], w[3]);
                     const int gy = ty0 + (pix >> 4), gx = tx0 + (pix & 15);
-                    inb[u] = gy < a.H && gx < a.W;
-                    vg[u] = vz[u] = make_uint4(0, 0, 0, 0);
-                    if (inb[u]) {
-                        const size_t o = ((size_t)gy * a.W + gx) * 64 + chunk * 8;
-                        vg[u] = *reinterpret_cast<const uint4 *>(a.g + o);
-                        vz[u] = __ldg(reinterpret_cast<const uint4 *>(a.z + o));
-                    }
+                    *reinterpret_cast<uint4 *>(a.g + ((size_t)gy * a.W + gx) * 64 + chunk * 8) = o;
                 }
-#pragma unroll
-                for (int u = 0; u < U; u++) {
-                    const int pix = (ptid >> 3) + 16 * (r0 + u);
-                    uint4 o = make_uint4(0, 0, 0, 0);
-                    if (inb[u]) {
-                        const uint32_t gw[4] = {vg[u].x, vg[u].y, vg[u].z, vg[u].w};
-                        const uint32_t zw[4] = {vz[u].x, vz[u].y, vz[u].z, vz[u].w};
-                        uint32_t w[4];
-#pragma unroll
-                        for (int j = 0; j < 4; j++) {
-                            const float2 gg = unpack_bf16(gw[j]), zz = unpack_bf16(zw[j]);
-                            w[j] = pack_bf16(fmaf(cA[2 * j], gg.x, fmaf(cB[2 * j], zz.x, cC[2 * j])),
-                                             fmaf(cA[2 * j + 1], gg.y, fmaf(cB[2 * j + 1], zz.y, cC[2 * j + 1])));
-                        }
-                        o = make_uint4(w[0], w[1], w[2], w[3]);
-                        const int gy = ty0 + (pix >> 4), gx = tx0 + (pix & 15);
-                        *reinterpret_cast<uint4 *>(a.g + ((size_t)gy * a.W + gx) * 64 + chunk * 8) = o;
-                    }
-                    *reinterpret_cast<uint4 *>(dstD + (pix >> 4) * D_R + chunk * D_S + (pix & 15) * 16) = o;
-                }
+                *reinterpret_cast<uint4 *>(dstD + (pix >> 4) * D_R + chunk * D_S + (pix & 15) * 16) = o;
+            }
             }
             fence_proxy_async();
             mbar_arrive(BAR(s));
@@ -586,14 +666,14 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a)
         const uint32_t a_hi = (uint32_t)(ad0 >> 32), b_hi = (uint32_t)(bd0 >> 32);
         int it = 0;
         for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it++) {
-            const int s = it & 1;
-            mbar_wait(BAR(s), (it >> 1) & 1);
+            const int s = it % STAGES;
+            mbar_wait(BAR(s), (it / STAGES) & 1);
             fence_after_sync();
             const uint32_t a_base = smem_u32(smem + s * STAGE);
             const uint32_t a_lo = (uint32_t)ad0 | ((a_base & 0x3FFFFu) >> 4);
             const uint32_t b_lo = (uint32_t)bd0 | (((a_base + A_BYTES) & 0x3FFFFu) >> 4);
 #pragma unroll
-            for (int r = 0; r < 16; r++) {
+            for (int r = 0; r < TR; r++) {
                 const uint64_t bd = ((uint64_t)b_hi << 32) | (b_lo + r * (D_R / 16));
 #pragma unroll
                 for (int j = 0; j < 6; j++) {
@@ -602,15 +682,15 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a)
                     mma_ss_el(tmem_base + j * 64, ad, bd, IDESC, (it | r) != 0, el);
                 }
             }
-            if (el) mma_commit(BAR(2 + s));
+            if (el) mma_commit(BAR(STAGES + s));
             __syncwarp();
         }
-        if (el) mma_commit(BAR(4));
+        if (el) mma_commit(BAR(2 * STAGES));
         __syncwarp();
     }
     fence_before_sync();
     __syncthreads();
-    if (warp == 8) tmem_dealloc(tmem_base, TMEM_COLS);
+    if (warp == MMA_WARP) tmem_dealloc(tmem_base, TMEM_COLS);
 }
 
 // dW[oc][ic][ky][kx] (+)= sum over CTA partials.  tap (ky,kx): ky < 2 -> accumulator kx, rows
@@ -778,7 +858,7 @@ int f2f_dncnn_wgrad64(const void *d_act, const float *d_coef_in, void *d_g, cons
     cudaStream_t st = (cudaStream_t)stream;
     wg::Args a;
     a.act = (const bf16 *)d_act; a.coef_in = d_coef_in; a.g = (bf16 *)d_g; a.z = (const bf16 *)d_z; a.coef = d_coef;
-    a.partial = d_partial; a.H = H; a.W = W; a.tiles_x = cdiv(W, 16); a.tiles_y = cdiv(H, 16);
+    a.partial = d_partial; a.H = H; a.W = W; a.tiles_x = cdiv(W, 16); a.tiles_y = cdiv(H, wg::TR);
     const int ntiles = a.tiles_x * a.tiles_y;
     const int grid = ntiles < num_sms() ? ntiles : num_sms();
     prof_begin(1, st);
@@ -804,7 +884,7 @@ int f2f_dncnn_backward(const float *d_params, float *d_grads, const float *d_dy,
     }
     static bool configured = false;
     if (!configured) {
-        F2F_CUDA_CHECK(cudaFuncSetAttribute(k_conv_last_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 88 * 4));
+        F2F_CUDA_CHECK(cudaFuncSetAttribute(k_conv_last_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, LBW_SMEM));
         F2F_CUDA_CHECK(cudaFuncSetAttribute(k_wgrad_first, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 72 * 4));
         configured = true;
     }
@@ -826,7 +906,7 @@ int f2f_dncnn_backward(const float *d_params, float *d_grads, const float *d_dy,
     F2F_CUDA_CHECK(cudaMemsetAsync(stats_b, 0, (pl.o_dw_small - pl.o_stats_b) + 1152 * 8, st));
     int cur = 0;   // gbuf[cur] holds g_k
     for (int b = 0; b < B; b++) {
-        k_conv_last_bwd<<<simt_blocks() / 2, 256, 64 * 88 * 4, st>>>(d_dy + b * P, residual ? -1.0f : 1.0f,
+        k_conv_last_bwd<<<num_sms(), 256, LBW_SMEM, st>>>(d_dy + b * P, residual ? -1.0f : 1.0f,
                                                                  zbuf(NBN) + b * P * 64, coef + (size_t)(NBN - 1) * C_STRIDE,
                                                                  d_params + OFF_W16, gbuf[cur] + b * P * 64,
                                                                  stats_b + (size_t)(NBN - 1) * 128, dw16, H, W);

@@ -136,3 +136,33 @@ def test_inline_division_is_ieee(cuda):
     bad = C.c_ulonglong(123)
     _lib.check(_lib.lib().f2f_selftest_division(1 << 30, C.byref(bad)), "selftest")
     assert bad.value == 0
+
+
+def test_tvl1flow_command_lines(cuda, tmp_path):
+    """The reference's command lines (main.c:86-99 positionals, tvl1flow.sh:9-19 sequence script) through
+    frame2frame_b200.tvl1flow_cli: .flo files byte-compatible with readFlowFile.py, flows equal to the oracle's."""
+    from PIL import Image
+    from frame2frame_b200 import tvl1flow_cli
+    from frame2frame_b200.tvl1 import read_flo
+    H, W = 72, 104
+    fr = [synth.noisy_frame(H, W, t) for t in range(3)]
+    for t, f in enumerate(fr):
+        Image.fromarray(f.astype(np.uint8)).save(str(tmp_path / ("f_%03d.png" % t)))
+    o = OracleTvl1()
+    # single pair, explicit positionals (nproc is accepted and ignored)
+    out = str(tmp_path / "a.flo")
+    assert tvl1flow_cli.main([str(tmp_path / "f_001.png"), str(tmp_path / "f_000.png"), out, "4", "0.25", "0.15", "0.3",
+                              "3", "0", "0.5", "5", "0.01", "0"]) == 0
+    u, _, _ = o.flow(fr[1], fr[0], nscales=3)
+    got = read_flo(out)
+    assert got.shape == (H, W, 2) and np.abs(got.transpose(2, 0, 1) - u).max() <= FLOW_TOL
+    # the sequence script: bflow / fflow of frames 0..1 with lambda 0.2, fscale 2
+    assert tvl1flow_cli.main(["--sequence", str(tmp_path / "f_%03d.png"), "0", "1", str(tmp_path / "o_%03d")]) == 0
+    kw = dict(lam=0.2, nscales=100, fscale=2)
+    for name, (a, b) in {"o_001_bflow.flo": (1, 0), "o_000_fflow.flo": (0, 1), "o_002_bflow.flo": (2, 1),
+                         "o_001_fflow.flo": (1, 2)}.items():
+        u, _, _ = o.flow(fr[a], fr[b], **kw)
+        assert np.abs(read_flo(str(tmp_path / name)).transpose(2, 0, 1) - u).max() <= FLOW_TOL, name
+    # size mismatch -> error return like main.c:189-193
+    Image.fromarray(fr[0][:40].astype(np.uint8)).save(str(tmp_path / "small.png"))
+    assert tvl1flow_cli.main([str(tmp_path / "small.png"), str(tmp_path / "f_000.png"), out]) == 1
