@@ -53,52 +53,6 @@ __global__ void k_prep_all(const float *__restrict__ params, bf16 *__restrict__ 
     wprep[idx] = __float2bfloat16(v);
 }
 
-// Conv(1->64, 3x3, pad 1) + ReLU (net.py:13-14): FP32 image -> NHWC BF16 activation.
-// 8 lanes per pixel, each lane 8 output channels (one 16-byte store; a pixel's 128 B are contiguous).
-__global__ void __launch_bounds__(256) k_conv_first(const float *__restrict__ x, const float *__restrict__ w0,
-                                                    bf16 *__restrict__ a0, int H, int W)
-{
-    const int chunk = threadIdx.x & 7;
-    float w[9][8];
-#pragma unroll
-    for (int t = 0; t < 9; t++)
-#pragma unroll
-        for (int j = 0; j < 8; j++) w[t][j] = w0[(chunk * 8 + j) * 9 + t];
-    const size_t P = (size_t)H * W;
-    constexpr int NP = 2;       // two pixels per thread and iteration, their 18 loads in flight together
-    for (size_t p0 = (size_t)blockIdx.x * (32 * NP) + (threadIdx.x >> 3); p0 < P; p0 += (size_t)gridDim.x * (32 * NP)) {
-        float xv[NP][9];
-#pragma unroll
-        for (int u = 0; u < NP; u++) {
-            const size_t p = p0 + 32 * u;
-            const int y = (int)(p / W), xx = (int)(p % W);
-#pragma unroll
-            for (int t = 0; t < 9; t++) {
-                const int yy = y + t / 3 - 1, xq = xx + t % 3 - 1;
-                xv[u][t] = (p < P && yy >= 0 && yy < H && xq >= 0 && xq < W) ? __ldg(x + (size_t)yy * W + xq) : 0.0f;
-            }
-        }
-#pragma unroll
-        for (int u = 0; u < NP; u++) {
-            const size_t p = p0 + 32 * u;
-            if (p >= P) continue;
-            float acc[8];
-#pragma unroll
-            for (int j = 0; j < 8; j++) acc[j] = 0.0f;
-#pragma unroll
-            for (int t = 0; t < 9; t++)
-#pragma unroll
-                for (int j = 0; j < 8; j++) acc[j] = fmaf(xv[u][t], w[t][j], acc[j]);
-            uint4 o;
-            o.x = pack_bf16(fmaxf(acc[0], 0.f), fmaxf(acc[1], 0.f));
-            o.y = pack_bf16(fmaxf(acc[2], 0.f), fmaxf(acc[3], 0.f));
-            o.z = pack_bf16(fmaxf(acc[4], 0.f), fmaxf(acc[5], 0.f));
-            o.w = pack_bf16(fmaxf(acc[6], 0.f), fmaxf(acc[7], 0.f));
-            *reinterpret_cast<uint4 *>(a0 + p * 64 + chunk * 8) = o;
-        }
-    }
-}
-
 // Train-mode BatchNorm2d bookkeeping of one layer: batch mean / biased variance from
 // the conv epilogue's sums, scale/shift for the next layer's operand staging, running-stat EMA
 // with the unbiased variance, num_batches_tracked.
@@ -159,262 +113,6 @@ __global__ void k_bn_bwd_coeffs(const double *__restrict__ stats, const float *_
     dbeta[c] = (accumulate ? dbeta[c] : 0.0f) + (float)db;
 }
 
-// Sums NV per-thread FP32 accumulators over the threads of the block that own the same
-// 8-channel chunk (lane % 8) and adds the result to double accumulators in global memory.
-// dst(i) maps value i of chunk `chunk` to its address.
-template <int NV, class F>
-__device__ __forceinline__ void block_chunk_reduce(float (&v)[NV], float *red /*[8 warps][8 chunks][NV]*/, F dst)
-{
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, chunk = threadIdx.x & 7;
-#pragma unroll
-    for (int i = 0; i < NV; i++) {
-        v[i] += __shfl_xor_sync(0xffffffffu, v[i], 8);
-        v[i] += __shfl_xor_sync(0xffffffffu, v[i], 16);
-    }
-    if (lane < 8) {
-#pragma unroll
-        for (int i = 0; i < NV; i++) red[(warp * 8 + chunk) * NV + i] = v[i];
-    }
-    __syncthreads();
-    for (int e = threadIdx.x; e < 8 * NV; e += blockDim.x) {
-        const int ch = e / NV, i = e % NV;
-        double t = 0.0;
-        for (int w = 0; w < 8; w++) t += (double)red[(w * 8 + ch) * NV + i];
-        atomicAdd(dst(ch, i), t);
-    }
-}
-
-// Conv(64->1, 3x3, pad 1) (net.py:19) with the BatchNorm+ReLU of layer 15 applied on load.
-// Every input pixel's 64 channels are read once: 8 lanes form the nine per-tap partial dot
-// products of that pixel, the output pixel then sums nine shifted partials from shared memory.
-// out = n (the noise estimate, SaoYan's forward) or x - n (net.py:31) when `residual`.
-constexpr int LT = 16, LH = LT + 2, LHP = LH * LH;
-constexpr int LBW_STRIDE = 76;     // floats between the per-chunk weight tables in shared memory (conflict-free 16-byte reads)
-__global__ void __launch_bounds__(256) k_conv_last(const bf16 *__restrict__ z, const float *__restrict__ coef,
-                                                   const float *__restrict__ w16, const float *__restrict__ x,
-                                                   float *__restrict__ out, int H, int W, int tiles_x, int ntiles,
-                                                   int residual)
-{
-    __shared__ float T[LHP * 9 + 4];
-    __shared__ __align__(16) float wS[8 * LBW_STRIDE];   // [chunk][tap][8 channels]: registers go to the loads in flight
-    const int chunk = threadIdx.x & 7;
-    for (int e = threadIdx.x; e < 8 * 72; e += 256) {
-        const int c = e / 72, t = (e % 72) >> 3, j = e & 7;
-        wS[c * LBW_STRIDE + t * 8 + j] = w16[(c * 8 + j) * 9 + t];
-    }
-    float sc[8], sh[8];
-#pragma unroll
-    for (int j = 0; j < 8; j++) { sc[j] = coef[C_SCALE + chunk * 8 + j]; sh[j] = coef[C_SHIFT + chunk * 8 + j]; }
-    __syncthreads();
-    const float4 *wv = reinterpret_cast<const float4 *>(wS + chunk * LBW_STRIDE);
-    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        const int ty0 = (tile / tiles_x) * LT, tx0 = (tile % tiles_x) * LT;
-        // the whole haloed tile's loads are issued before any arithmetic (one exposed memory latency per tile, not eleven)
-        constexpr int ROUNDS = (LHP * 8 + 255) / 256;
-        uint4 v[ROUNDS];
-        uint32_t okm = 0;
-#pragma unroll
-        for (int r = 0; r < ROUNDS; r++) {
-            const int pix = (threadIdx.x + 256 * r) >> 3;
-            const int gy = ty0 - 1 + pix / LH, gx = tx0 - 1 + pix % LH;
-            v[r] = make_uint4(0, 0, 0, 0);
-            if (pix < LHP && gy >= 0 && gy < H && gx >= 0 && gx < W) {
-                okm |= 1u << r;
-                v[r] = __ldg(reinterpret_cast<const uint4 *>(z + ((size_t)gy * W + gx) * 64 + chunk * 8));
-            }
-        }
-#pragma unroll
-        for (int r = 0; r < ROUNDS; r++) {
-            const int pix = (threadIdx.x + 256 * r) >> 3;
-            float part[9];
-#pragma unroll
-            for (int t = 0; t < 9; t++) part[t] = 0.0f;
-            if ((okm >> r) & 1u) {
-                const uint32_t vw[4] = {v[r].x, v[r].y, v[r].z, v[r].w};
-                float a[8];
-#pragma unroll
-                for (int q = 0; q < 4; q++) {
-                    const float2 f = unpack_bf16(vw[q]);
-                    a[2 * q] = fmaxf(fmaf(f.x, sc[2 * q], sh[2 * q]), 0.0f);
-                    a[2 * q + 1] = fmaxf(fmaf(f.y, sc[2 * q + 1], sh[2 * q + 1]), 0.0f);
-                }
-#pragma unroll
-                for (int t = 0; t < 9; t++) {
-                    const float4 w0 = wv[2 * t], w1 = wv[2 * t + 1];
-                    part[t] = fmaf(a[0], w0.x, fmaf(a[1], w0.y, fmaf(a[2], w0.z, fmaf(a[3], w0.w, 0.0f)))) +
-                              fmaf(a[4], w1.x, fmaf(a[5], w1.y, fmaf(a[6], w1.z, fmaf(a[7], w1.w, 0.0f))));
-                }
-            }
-            // every lane takes part in the shuffles (groups of 8 lanes share a pixel); only the store is guarded
-#pragma unroll
-            for (int t = 0; t < 9; t++) {
-                part[t] += __shfl_xor_sync(0xffffffffu, part[t], 1);
-                part[t] += __shfl_xor_sync(0xffffffffu, part[t], 2);
-                part[t] += __shfl_xor_sync(0xffffffffu, part[t], 4);
-            }
-            // lane c of the group stores tap c (lane 0 also tap 8)
-            float mine = part[0];
-#pragma unroll
-            for (int t = 1; t < 8; t++) mine = (chunk == t) ? part[t] : mine;
-            if (pix < LHP) {
-                T[pix * 9 + chunk] = mine;
-                if (chunk == 0) T[pix * 9 + 8] = part[8];
-            }
-        }
-        __syncthreads();
-        {
-            const int y = threadIdx.x >> 4, xx = threadIdx.x & 15;
-            const int gy = ty0 + y, gx = tx0 + xx;
-            float n = 0.0f;
-#pragma unroll
-            for (int t = 0; t < 9; t++) n += T[((y + t / 3) * LH + xx + t % 3) * 9 + t];
-            if (gy < H && gx < W) {
-                const size_t i = (size_t)gy * W + gx;
-                out[i] = residual ? x[i] - n : n;
-            }
-        }
-        __syncthreads();
-    }
-}
-
-// Backward of the last layer: input gradient (1->64 transposed conv) masked by layer 15's ReLU,
-// its BatchNorm-backward sums, and the last layer's weight gradient -- one pass over z15.
-//   g15[q][ic]      = relu'(.) * sum_k dn[q - k + 1] * w16[ic][k]
-//   dW16[ic][k]     = sum_q a15[q][ic] * dn[q - k + 1]
-constexpr int LBW_SMEM = 64 * 88 * 4 + 8 * LBW_STRIDE * 4;
-__global__ void __launch_bounds__(256, 1) k_conv_last_bwd(const float *__restrict__ dy, float dy_sign,
-                                                          const bf16 *__restrict__ z, const float *__restrict__ coef,
-                                                          const float *__restrict__ w16, bf16 *__restrict__ g,
-                                                          double *__restrict__ stats, double *__restrict__ dw16, int H,
-                                                          int W)
-{
-    extern __shared__ float red[];
-    float *wS = red + 64 * 88;                   // [chunk][tap][8 channels]
-    const int chunk = threadIdx.x & 7;
-    for (int e = threadIdx.x; e < 8 * 72; e += 256) {
-        const int c = e / 72, t = (e % 72) >> 3, j = e & 7;
-        wS[c * LBW_STRIDE + t * 8 + j] = w16[(c * 8 + j) * 9 + t];
-    }
-    float sc[8], sh[8], mu[8], is[8];
-#pragma unroll
-    for (int j = 0; j < 8; j++) {
-        sc[j] = coef[C_SCALE + chunk * 8 + j]; sh[j] = coef[C_SHIFT + chunk * 8 + j];
-        mu[j] = coef[C_MEAN + chunk * 8 + j]; is[j] = coef[C_INVSTD + chunk * 8 + j];
-    }
-    __syncthreads();
-    const float4 *wv = reinterpret_cast<const float4 *>(wS + chunk * LBW_STRIDE);
-    float acc[88];   // [0,72): dW16[tap][j]; [72,80): sum g; [80,88): sum g*xhat
-#pragma unroll
-    for (int i = 0; i < 88; i++) acc[i] = 0.0f;
-    const size_t P = (size_t)H * W;
-    // Two pixels per thread and iteration, all their loads issued before any arithmetic: with 8 warps per SM
-    // (the 88 accumulators bound the occupancy) the loop is otherwise one exposed DRAM latency per pixel.
-    constexpr int NP = 2;
-    for (size_t p0 = (size_t)blockIdx.x * (32 * NP) + (threadIdx.x >> 3); p0 < P; p0 += (size_t)gridDim.x * (32 * NP)) {
-        uint4 v[NP];
-        float dn[NP][9];
-        bool ok[NP];
-#pragma unroll
-        for (int u = 0; u < NP; u++) {
-            const size_t p = p0 + 32 * u;
-            ok[u] = p < P;
-            v[u] = make_uint4(0, 0, 0, 0);
-            if (ok[u]) v[u] = __ldg(reinterpret_cast<const uint4 *>(z + p * 64 + chunk * 8));
-            const int y = (int)(p / W), xx = (int)(p % W);
-#pragma unroll
-            for (int t = 0; t < 9; t++) {
-                const int yy = y - (t / 3) + 1, xq = xx - (t % 3) + 1;
-                dn[u][t] = (ok[u] && yy >= 0 && yy < H && xq >= 0 && xq < W) ? dy_sign * __ldg(dy + (size_t)yy * W + xq) : 0.0f;
-            }
-        }
-#pragma unroll
-        for (int u = 0; u < NP; u++) {
-            if (!ok[u]) continue;
-            const size_t p = p0 + 32 * u;
-            const uint32_t vw[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
-            float zz[8], a[8], s[8];
-#pragma unroll
-            for (int q = 0; q < 4; q++) { const float2 f = unpack_bf16(vw[q]); zz[2 * q] = f.x; zz[2 * q + 1] = f.y; }
-#pragma unroll
-            for (int j = 0; j < 8; j++) { a[j] = fmaf(zz[j], sc[j], sh[j]); s[j] = 0.0f; }   // a = pre-ReLU BN output for now
-#pragma unroll
-            for (int t = 0; t < 9; t++) {
-                const float4 w0 = wv[2 * t], w1 = wv[2 * t + 1];
-                const float wt[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
-#pragma unroll
-                for (int j = 0; j < 8; j++) {
-                    s[j] = fmaf(dn[u][t], wt[j], s[j]);
-                    acc[t * 8 + j] = fmaf(fmaxf(a[j], 0.0f), dn[u][t], acc[t * 8 + j]);
-                }
-            }
-            float gg[8];
-#pragma unroll
-            for (int j = 0; j < 8; j++) gg[j] = a[j] > 0.0f ? s[j] : 0.0f;
-            uint4 o;
-            o.x = pack_bf16(gg[0], gg[1]); o.y = pack_bf16(gg[2], gg[3]);
-            o.z = pack_bf16(gg[4], gg[5]); o.w = pack_bf16(gg[6], gg[7]);
-            *reinterpret_cast<uint4 *>(g + p * 64 + chunk * 8) = o;
-            const uint32_t ow[4] = {o.x, o.y, o.z, o.w};
-#pragma unroll
-            for (int q = 0; q < 4; q++) {                  // sums of the ROUNDED gradient, like the tcgen05 epilogue
-                const float2 f = unpack_bf16(ow[q]);
-                acc[72 + 2 * q] += f.x; acc[72 + 2 * q + 1] += f.y;
-                acc[80 + 2 * q] = fmaf(f.x, (zz[2 * q] - mu[2 * q]) * is[2 * q], acc[80 + 2 * q]);
-                acc[80 + 2 * q + 1] = fmaf(f.y, (zz[2 * q + 1] - mu[2 * q + 1]) * is[2 * q + 1], acc[80 + 2 * q + 1]);
-            }
-        }
-    }
-    __syncthreads();
-    block_chunk_reduce<88>(acc, red, [&](int ch, int i) -> double * {
-        if (i < 72) return dw16 + (ch * 8 + (i & 7)) * 9 + (i >> 3);
-        if (i < 80) return stats + ch * 8 + (i - 72);
-        return stats + 64 + ch * 8 + (i - 80);
-    });
-}
-
-// Weight gradient of the first layer: dW0[oc][k] = sum_p g0[p][oc] * x[p + k - 1]  (g0 already ReLU-masked)
-__global__ void __launch_bounds__(256, 1) k_wgrad_first(const bf16 *__restrict__ g0, const float *__restrict__ x,
-                                                        double *__restrict__ dw0, int H, int W)
-{
-    extern __shared__ float red[];
-    const int chunk = threadIdx.x & 7;
-    float acc[72];
-#pragma unroll
-    for (int i = 0; i < 72; i++) acc[i] = 0.0f;
-    const size_t P = (size_t)H * W;
-    constexpr int NP = 2;       // two pixels per thread and iteration, all their loads in flight together
-    for (size_t p0 = (size_t)blockIdx.x * (32 * NP) + (threadIdx.x >> 3); p0 < P; p0 += (size_t)gridDim.x * (32 * NP)) {
-        float xv[NP][9];
-        uint4 v[NP];
-#pragma unroll
-        for (int u = 0; u < NP; u++) {
-            const size_t p = p0 + 32 * u;
-            const int y = (int)(p / W), xx = (int)(p % W);
-            v[u] = make_uint4(0, 0, 0, 0);          // a zero gradient adds nothing: out-of-range pixels need no branch below
-            if (p < P) v[u] = __ldg(reinterpret_cast<const uint4 *>(g0 + p * 64 + chunk * 8));
-#pragma unroll
-            for (int t = 0; t < 9; t++) {
-                const int yy = y + t / 3 - 1, xq = xx + t % 3 - 1;
-                xv[u][t] = (p < P && yy >= 0 && yy < H && xq >= 0 && xq < W) ? __ldg(x + (size_t)yy * W + xq) : 0.0f;
-            }
-        }
-#pragma unroll
-        for (int u = 0; u < NP; u++) {
-            const uint32_t vw[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
-#pragma unroll
-            for (int q = 0; q < 4; q++) {
-                const float2 f = unpack_bf16(vw[q]);
-#pragma unroll
-                for (int t = 0; t < 9; t++) {
-                    acc[t * 8 + 2 * q] = fmaf(f.x, xv[u][t], acc[t * 8 + 2 * q]);
-                    acc[t * 8 + 2 * q + 1] = fmaf(f.y, xv[u][t], acc[t * 8 + 2 * q + 1]);
-                }
-            }
-        }
-    }
-    block_chunk_reduce<72>(acc, red, [&](int ch, int i) -> double * { return dw0 + (ch * 8 + (i & 7)) * 9 + (i >> 3); });
-}
-
 __global__ void k_small_grads(const double *__restrict__ dw0, const double *__restrict__ dw16, float *__restrict__ grads,
                               int accumulate)
 {
@@ -441,6 +139,281 @@ __global__ void k_adam(float *__restrict__ p, const float *__restrict__ g, float
         p[i] = pi - step_size * (mi / denom);                // param.addcdiv_(exp_avg, denom, value=-step_size)
     }
 }
+
+// ------------------------------------------------ first / last layer, row-streaming formulation
+// The 1<->64-channel layers (net.py:13-14,19 and their backward) are HBM-bound by design: 128 B per pixel read or
+// written.  A first formulation with 8 lanes per pixel and 8 channels per lane needed 72-88 accumulators per thread
+// (8 warps per SM) and exposed one memory latency per pixel: 250 / 270 / 595 / 205 us at 1080p.
+// Here a LANE OWNS TWO CHANNELS: a warp reads or writes one pixel's 128 contiguous bytes per step, the per-tap
+// accumulators are 18 registers, and the 64-channel image streams through shared memory in 8-row x 64-pixel tiles
+// fetched by the bulk-copy engine one tile ahead (64 KB in flight per SM without holding a register).
+constexpr int LT = 16, LH = LT + 2, LHP = LH * LH;   // output tile / haloed tile of the 64->1 layer
+
+namespace rs {
+constexpr int TW = 64, TH = 8, NT = 512;            // tile, threads per block (16 warps: row = warp / 2, half = warp & 1)
+constexpr int ZROW = TW * 128, ZSTAGE = TH * ZROW;  // one staged row / tile of the NHWC BF16 image
+constexpr int XW = TW + 2, XH = TH + 2;             // haloed FP32 tile of the 1-channel image
+constexpr int OFF_X = 2 * ZSTAGE, OFF_BAR = OFF_X + ((XH * XW * 4 + 15) & ~15);
+constexpr int SMEM = OFF_BAR + 16;
+
+// thread 0: rows of tile (ty0, tx0) of `img` -> stage at `dst`, completion on `bar`
+__device__ __forceinline__ void stage_tile(uint32_t dst, uint32_t bar, const bf16 *img, int ty0, int tx0, int H, int W)
+{
+    const int rows = min(TH, H - ty0), nx = min(TW, W - tx0);
+    fence_proxy_async();                                  // the stage was last read through the generic proxy
+    mbar_arrive_expect_tx(bar, (uint32_t)(rows * nx * 128));
+    for (int r = 0; r < rows; r++)
+        bulk_g2s(dst + r * ZROW, img + ((size_t)(ty0 + r) * W + tx0) * 64, (uint32_t)(nx * 128), bar);
+}
+
+// haloed FP32 tile, zero outside the image, scaled by `mul`
+__device__ __forceinline__ void load_halo(float *xS, const float *__restrict__ img, float mul, int ty0, int tx0, int H, int W)
+{
+    for (int i = threadIdx.x; i < XH * XW; i += NT) {
+        const int yy = ty0 - 1 + i / XW, xx = tx0 - 1 + i % XW;
+        xS[i] = (yy >= 0 && yy < H && xx >= 0 && xx < W) ? mul * __ldg(img + (size_t)yy * W + xx) : 0.0f;
+    }
+}
+
+// sums NV per-lane values over the 16 warps (scratch: NT * NV floats) and adds channel pair sums to FP64 accumulators
+template <int NV, class F>
+__device__ __forceinline__ void block_pair_reduce(const float (&v)[NV], float *scratch, F dst)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int i = 0; i < NV; i++) scratch[(warp * NV + i) * 32 + lane] = v[i];
+    __syncthreads();
+    for (int e = threadIdx.x; e < 32 * NV; e += NT) {
+        const int i = e >> 5, l = e & 31;
+        double t = 0.0;
+        for (int w = 0; w < NT / 32; w++) t += (double)scratch[(w * NV + i) * 32 + l];
+        atomicAdd(dst(l, i), t);
+    }
+}
+
+// Backward of the last layer: input gradient (1->64 transposed conv) masked by layer 15's ReLU, its
+// BatchNorm-backward sums, and the last layer's weight gradient -- one pass over z15.
+//   g15[q][ic]  = relu'(.) * sum_k dn[q - k + 1] * w16[ic][k]        dW16[ic][k] = sum_q a15[q][ic] * dn[q - k + 1]
+__global__ void __launch_bounds__(NT, 1) k_last_bwd(const float *__restrict__ dy, float dy_sign, const bf16 *__restrict__ z,
+                                                    const float *__restrict__ coef, const float *__restrict__ w16,
+                                                    bf16 *__restrict__ g, double *__restrict__ stats,
+                                                    double *__restrict__ dw16, int H, int W, int tiles_x, int ntiles)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    float *dnS = reinterpret_cast<float *>(smem + OFF_X);
+    const uint32_t bar0 = smem_u32(smem + OFF_BAR);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, r = warp >> 1, xh = (warp & 1) * 32, c0 = 2 * lane;
+    if (threadIdx.x == 0) { mbar_init(bar0, 1); mbar_init(bar0 + 8, 1); mbar_fence_init(); }
+    float w[9][2], sc[2], sh[2], is[2], ms[2];
+#pragma unroll
+    for (int j = 0; j < 2; j++) {
+#pragma unroll
+        for (int t = 0; t < 9; t++) w[t][j] = w16[(c0 + j) * 9 + t];
+        sc[j] = coef[C_SCALE + c0 + j]; sh[j] = coef[C_SHIFT + c0 + j];
+        is[j] = coef[C_INVSTD + c0 + j]; ms[j] = -coef[C_MEAN + c0 + j] * is[j];     // xhat = z * is + ms
+    }
+    float acc[22];   // [0,18): dW16[tap][j]; [18,20): sum g; [20,22): sum g*xhat
+#pragma unroll
+    for (int i = 0; i < 22; i++) acc[i] = 0.0f;
+    __syncthreads();
+    if (threadIdx.x == 0 && blockIdx.x < ntiles)
+        stage_tile(smem_u32(smem), bar0, z, (blockIdx.x / tiles_x) * TH, (blockIdx.x % tiles_x) * TW, H, W);
+    int it = 0;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it++) {
+        const int s = it & 1, ty0 = (tile / tiles_x) * TH, tx0 = (tile % tiles_x) * TW;
+        const int next = tile + gridDim.x;
+        if (threadIdx.x == 0 && next < ntiles)
+            stage_tile(smem_u32(smem + (s ^ 1) * ZSTAGE), bar0 + 8 * (s ^ 1), z, (next / tiles_x) * TH, (next % tiles_x) * TW, H, W);
+        load_halo(dnS, dy, dy_sign, ty0, tx0, H, W);
+        __syncthreads();
+        mbar_wait(bar0 + 8 * s, (it >> 1) & 1);
+        const int y = ty0 + r, nx = min(TW, W - tx0);
+        if (y < H) {
+            const uint8_t *zrow = smem + s * ZSTAGE + r * ZROW + lane * 4;
+            bf16 *grow = g + ((size_t)y * W + tx0) * 64 + c0;
+            const float *d2 = dnS + (r + 2) * XW + 2;       // dn[ky][kx] at d2[-ky * XW - kx + x]
+#pragma unroll 4
+            for (int x = xh; x < min(xh + 32, nx); x++) {
+                const float2 zz = unpack_bf16(*reinterpret_cast<const uint32_t *>(zrow + x * 128));
+                const float y0 = fmaf(zz.x, sc[0], sh[0]), y1 = fmaf(zz.y, sc[1], sh[1]);
+                const float a0 = fmaxf(y0, 0.0f), a1 = fmaxf(y1, 0.0f);
+                float s0 = 0.0f, s1 = 0.0f;
+#pragma unroll
+                for (int t = 0; t < 9; t++) {
+                    const float dn = d2[x - (t / 3) * XW - (t % 3)];
+                    s0 = fmaf(dn, w[t][0], s0); s1 = fmaf(dn, w[t][1], s1);
+                    acc[2 * t] = fmaf(a0, dn, acc[2 * t]); acc[2 * t + 1] = fmaf(a1, dn, acc[2 * t + 1]);
+                }
+                const uint32_t o = pack_bf16(y0 > 0.0f ? s0 : 0.0f, y1 > 0.0f ? s1 : 0.0f);
+                *reinterpret_cast<uint32_t *>(grow + (size_t)x * 64) = o;
+                const float2 gr = unpack_bf16(o);             // sums of the ROUNDED gradient, like the tcgen05 epilogue
+                acc[18] += gr.x; acc[19] += gr.y;
+                acc[20] = fmaf(gr.x, fmaf(zz.x, is[0], ms[0]), acc[20]);
+                acc[21] = fmaf(gr.y, fmaf(zz.y, is[1], ms[1]), acc[21]);
+            }
+        }
+        __syncthreads();                                     // stage s and dnS are free again
+    }
+    block_pair_reduce<22>(acc, reinterpret_cast<float *>(smem), [&](int l, int i) -> double * {
+        if (i < 18) return dw16 + (2 * l + (i & 1)) * 9 + (i >> 1);
+        if (i < 20) return stats + 2 * l + (i - 18);
+        return stats + 64 + 2 * l + (i - 20);
+    });
+}
+
+// Weight gradient of the first layer: dW0[oc][k] = sum_p g0[p][oc] * x[p + k - 1]
+__global__ void __launch_bounds__(NT, 1) k_first_wgrad(const bf16 *__restrict__ g0, const float *__restrict__ x,
+                                                       double *__restrict__ dw0, int H, int W, int tiles_x, int ntiles)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    float *xS = reinterpret_cast<float *>(smem + OFF_X);
+    const uint32_t bar0 = smem_u32(smem + OFF_BAR);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, r = warp >> 1, xh = (warp & 1) * 32;
+    if (threadIdx.x == 0) { mbar_init(bar0, 1); mbar_init(bar0 + 8, 1); mbar_fence_init(); }
+    float acc[18];
+#pragma unroll
+    for (int i = 0; i < 18; i++) acc[i] = 0.0f;
+    __syncthreads();
+    if (threadIdx.x == 0 && blockIdx.x < ntiles)
+        stage_tile(smem_u32(smem), bar0, g0, (blockIdx.x / tiles_x) * TH, (blockIdx.x % tiles_x) * TW, H, W);
+    int it = 0;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it++) {
+        const int s = it & 1, ty0 = (tile / tiles_x) * TH, tx0 = (tile % tiles_x) * TW;
+        const int next = tile + gridDim.x;
+        if (threadIdx.x == 0 && next < ntiles)
+            stage_tile(smem_u32(smem + (s ^ 1) * ZSTAGE), bar0 + 8 * (s ^ 1), g0, (next / tiles_x) * TH, (next % tiles_x) * TW, H, W);
+        load_halo(xS, x, 1.0f, ty0, tx0, H, W);
+        __syncthreads();
+        mbar_wait(bar0 + 8 * s, (it >> 1) & 1);
+        const int y = ty0 + r, nx = min(TW, W - tx0);
+        if (y < H) {
+            const uint8_t *grow = smem + s * ZSTAGE + r * ZROW + lane * 4;
+            const float *x0 = xS + r * XW;                   // x[p + (ky-1, kx-1)] at x0[ky * XW + kx + x]
+#pragma unroll 4
+            for (int x_ = xh; x_ < min(xh + 32, nx); x_++) {
+                const float2 gg = unpack_bf16(*reinterpret_cast<const uint32_t *>(grow + x_ * 128));
+#pragma unroll
+                for (int t = 0; t < 9; t++) {
+                    const float xv = x0[x_ + (t / 3) * XW + (t % 3)];
+                    acc[2 * t] = fmaf(gg.x, xv, acc[2 * t]); acc[2 * t + 1] = fmaf(gg.y, xv, acc[2 * t + 1]);
+                }
+            }
+        }
+        __syncthreads();
+    }
+    block_pair_reduce<18>(acc, reinterpret_cast<float *>(smem),
+                          [&](int l, int i) -> double * { return dw0 + (2 * l + (i & 1)) * 9 + (i >> 1); });
+}
+
+// Conv(1->64, 3x3, pad 1) + ReLU (net.py:13-14): FP32 image -> NHWC BF16 activation; a warp writes one pixel's 128 bytes per step.
+constexpr int FT = 256;                              // 8 warps: warp = tile row
+__global__ void __launch_bounds__(FT) k_first_fwd(const float *__restrict__ x, const float *__restrict__ w0, bf16 *__restrict__ a0,
+                                                  int H, int W, int tiles_x, int ntiles)
+{
+    __shared__ float xS[XH * XW];
+    const int lane = threadIdx.x & 31, r = threadIdx.x >> 5, c0 = 2 * lane;
+    float w[9][2];
+#pragma unroll
+    for (int j = 0; j < 2; j++)
+#pragma unroll
+        for (int t = 0; t < 9; t++) w[t][j] = w0[(c0 + j) * 9 + t];
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const int ty0 = (tile / tiles_x) * TH, tx0 = (tile % tiles_x) * TW;
+        __syncthreads();
+        for (int i = threadIdx.x; i < XH * XW; i += FT) {
+            const int yy = ty0 - 1 + i / XW, xx = tx0 - 1 + i % XW;
+            xS[i] = (yy >= 0 && yy < H && xx >= 0 && xx < W) ? __ldg(x + (size_t)yy * W + xx) : 0.0f;
+        }
+        __syncthreads();
+        const int y = ty0 + r, nx = min(TW, W - tx0);
+        if (y >= H) continue;
+        const float *x0 = xS + r * XW;
+        bf16 *orow = a0 + ((size_t)y * W + tx0) * 64 + c0;
+#pragma unroll 4
+        for (int x_ = 0; x_ < nx; x_++) {
+            float s0 = 0.0f, s1 = 0.0f;
+#pragma unroll
+            for (int t = 0; t < 9; t++) {
+                const float xv = x0[x_ + (t / 3) * XW + (t % 3)];
+                s0 = fmaf(xv, w[t][0], s0); s1 = fmaf(xv, w[t][1], s1);
+            }
+            *reinterpret_cast<uint32_t *>(orow + (size_t)x_ * 64) = pack_bf16(fmaxf(s0, 0.0f), fmaxf(s1, 0.0f));
+        }
+    }
+}
+
+// Conv(64->1, 3x3, pad 1) (net.py:19) with layer 15's BatchNorm+ReLU on load; out = n (the noise estimate,
+// SaoYan's forward) or x - n (net.py:31) when `residual`.  ONE LANE PER INPUT PIXEL of the
+// haloed 18x18 tile: the lane reads its pixel's 128 bytes (eight 16-byte loads in flight), forms the nine per-tap
+// dot products over all 64 channels with no cross-lane reduction (weights and coefficients are warp-uniform
+// shared-memory reads), and the output pixel sums nine shifted partials from shared memory.
+__global__ void __launch_bounds__(256) k_last_fwd(const bf16 *__restrict__ z, const float *__restrict__ coef,
+                                                  const float *__restrict__ w16, const float *__restrict__ x,
+                                                  float *__restrict__ out, int H, int W, int tiles_x, int ntiles, int residual)
+{
+    __shared__ float T[LHP * 9 + 4];
+    __shared__ __align__(16) float wS[8 * 72];          // [chunk][tap][8 channels]
+    __shared__ __align__(16) float cS[128];             // scale[64], shift[64]
+    for (int e = threadIdx.x; e < 8 * 72; e += 256) {
+        const int c = e / 72, t = (e % 72) >> 3, j = e & 7;
+        wS[e] = w16[(c * 8 + j) * 9 + t];
+    }
+    if (threadIdx.x < 64) { cS[threadIdx.x] = coef[C_SCALE + threadIdx.x]; cS[64 + threadIdx.x] = coef[C_SHIFT + threadIdx.x]; }
+    __syncthreads();
+    const float4 *wv = reinterpret_cast<const float4 *>(wS), *cv = reinterpret_cast<const float4 *>(cS);
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const int ty0 = (tile / tiles_x) * LT, tx0 = (tile % tiles_x) * LT;
+#pragma unroll 1
+        for (int pix = threadIdx.x; pix < LHP; pix += 256) {
+            const int gy = ty0 - 1 + pix / LH, gx = tx0 - 1 + pix % LH;
+            float part[9];
+#pragma unroll
+            for (int t = 0; t < 9; t++) part[t] = 0.0f;
+            if (gy >= 0 && gy < H && gx >= 0 && gx < W) {
+                const uint4 *src = reinterpret_cast<const uint4 *>(z + ((size_t)gy * W + gx) * 64);
+                uint4 v[8];
+#pragma unroll
+                for (int c = 0; c < 8; c++) v[c] = __ldg(src + c);
+#pragma unroll
+                for (int c = 0; c < 8; c++) {
+                    const uint32_t vw[4] = {v[c].x, v[c].y, v[c].z, v[c].w};
+                    const float4 s0 = cv[2 * c], s1 = cv[2 * c + 1], h0 = cv[16 + 2 * c], h1 = cv[16 + 2 * c + 1];
+                    const float scv[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+                    const float shv[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+                    float a[8];
+#pragma unroll
+                    for (int q = 0; q < 4; q++) {
+                        const float2 f = unpack_bf16(vw[q]);
+                        a[2 * q] = fmaxf(fmaf(f.x, scv[2 * q], shv[2 * q]), 0.0f);
+                        a[2 * q + 1] = fmaxf(fmaf(f.y, scv[2 * q + 1], shv[2 * q + 1]), 0.0f);
+                    }
+#pragma unroll
+                    for (int t = 0; t < 9; t++) {
+                        const float4 w0 = wv[c * 18 + 2 * t], w1 = wv[c * 18 + 2 * t + 1];
+                        part[t] = fmaf(a[0], w0.x, fmaf(a[1], w0.y, fmaf(a[2], w0.z, fmaf(a[3], w0.w, part[t]))));
+                        part[t] = fmaf(a[4], w1.x, fmaf(a[5], w1.y, fmaf(a[6], w1.z, fmaf(a[7], w1.w, part[t]))));
+                    }
+                }
+            }
+#pragma unroll
+            for (int t = 0; t < 9; t++) T[pix * 9 + t] = part[t];
+        }
+        __syncthreads();
+        {
+            const int y = threadIdx.x >> 4, xx = threadIdx.x & 15;
+            const int gy = ty0 + y, gx = tx0 + xx;
+            float n = 0.0f;
+#pragma unroll
+            for (int t = 0; t < 9; t++) n += T[((y + t / 3) * LH + xx + t % 3) * 9 + t];
+            if (gy < H && gx < W) {
+                const size_t i = (size_t)gy * W + gx;
+                out[i] = residual ? x[i] - n : n;
+            }
+        }
+        __syncthreads();
+    }
+}
+}  // namespace rs
 
 // ------------------------------------------------------- tcgen05 weight gradient
 // dW[oc][ic][ky][kx] = sum_p dz[p][oc] * a[p + (ky-1, kx-1)][ic]   (a = the layer's input activation)
@@ -812,7 +785,9 @@ int f2f_dncnn_forward(const float *d_params, float *d_bn_running, long long *d_n
         g_dncnn_launches++;
     }
     for (int b = 0; b < B; b++) {
-        k_conv_first<<<simt_blocks(), 256, 0, st>>>(d_x + b * P, d_params + OFF_W0, a0 + b * P * 64, H, W);
+        const int rtx = cdiv(W, rs::TW), rnt = rtx * cdiv(H, rs::TH);
+        rs::k_first_fwd<<<rnt < num_sms() * 6 ? rnt : num_sms() * 6, rs::FT, 0, st>>>(d_x + b * P, d_params + OFF_W0,
+                                                                                    a0 + b * P * 64, H, W, rtx, rnt);
         g_dncnn_launches++;
     }
     F2F_LAUNCH_CHECK();
@@ -834,7 +809,7 @@ int f2f_dncnn_forward(const float *d_params, float *d_bn_running, long long *d_n
     }
     const int tiles_x = cdiv(W, LT), ntiles = tiles_x * cdiv(H, LT);
     for (int b = 0; b < B; b++) {
-        k_conv_last<<<ntiles < simt_blocks() ? ntiles : simt_blocks(), 256, 0, st>>>(
+        rs::k_last_fwd<<<ntiles < simt_blocks() ? ntiles : simt_blocks(), 256, 0, st>>>(
             zbuf(NBN) + b * P * 64, coef + (size_t)(NBN - 1) * C_STRIDE, d_params + OFF_W16, d_x + b * P, d_y + b * P, H, W,
             tiles_x, ntiles, residual);
         g_dncnn_launches++;
@@ -884,8 +859,8 @@ int f2f_dncnn_backward(const float *d_params, float *d_grads, const float *d_dy,
     }
     static bool configured = false;
     if (!configured) {
-        F2F_CUDA_CHECK(cudaFuncSetAttribute(k_conv_last_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, LBW_SMEM));
-        F2F_CUDA_CHECK(cudaFuncSetAttribute(k_wgrad_first, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 72 * 4));
+        F2F_CUDA_CHECK(cudaFuncSetAttribute(rs::k_last_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, rs::SMEM));
+        F2F_CUDA_CHECK(cudaFuncSetAttribute(rs::k_first_wgrad, cudaFuncAttributeMaxDynamicSharedMemorySize, rs::SMEM));
         configured = true;
     }
     cudaStream_t st = (cudaStream_t)stream;
@@ -905,11 +880,11 @@ int f2f_dncnn_backward(const float *d_params, float *d_grads, const float *d_dy,
     // stats_b and the small double accumulators are adjacent (make_plan)
     F2F_CUDA_CHECK(cudaMemsetAsync(stats_b, 0, (pl.o_dw_small - pl.o_stats_b) + 1152 * 8, st));
     int cur = 0;   // gbuf[cur] holds g_k
+    const int rtx = cdiv(W, rs::TW), rnt = rtx * cdiv(H, rs::TH);
     for (int b = 0; b < B; b++) {
-        k_conv_last_bwd<<<num_sms(), 256, LBW_SMEM, st>>>(d_dy + b * P, residual ? -1.0f : 1.0f,
-                                                                 zbuf(NBN) + b * P * 64, coef + (size_t)(NBN - 1) * C_STRIDE,
-                                                                 d_params + OFF_W16, gbuf[cur] + b * P * 64,
-                                                                 stats_b + (size_t)(NBN - 1) * 128, dw16, H, W);
+        rs::k_last_bwd<<<rnt < num_sms() ? rnt : num_sms(), rs::NT, rs::SMEM, st>>>(
+            d_dy + b * P, residual ? -1.0f : 1.0f, zbuf(NBN) + b * P * 64, coef + (size_t)(NBN - 1) * C_STRIDE,
+            d_params + OFF_W16, gbuf[cur] + b * P * 64, stats_b + (size_t)(NBN - 1) * 128, dw16, H, W, rtx, rnt);
         g_dncnn_launches++;
     }
     F2F_LAUNCH_CHECK();
@@ -944,7 +919,8 @@ int f2f_dncnn_backward(const float *d_params, float *d_grads, const float *d_dy,
     }
     dump(30, gbuf[cur]);
     for (int b = 0; b < B; b++) {
-        k_wgrad_first<<<simt_blocks() / 2, 256, 64 * 72 * 4, st>>>(gbuf[cur] + b * P * 64, x + b * P, dw0, H, W);
+        rs::k_first_wgrad<<<rnt < num_sms() ? rnt : num_sms(), rs::NT, rs::SMEM, st>>>(gbuf[cur] + b * P * 64, x + b * P, dw0, H,
+                                                                                       W, rtx, rnt);
         g_dncnn_launches++;
     }
     k_small_grads<<<cdiv(1152, 256), 256, 0, st>>>(dw0, dw16, d_grads, accumulate);
