@@ -60,9 +60,10 @@ def reference_arm(args, rank, world):
     import numpy as np
     from oracle.tvl1 import OracleTvl1, RefTvl1
     cores = os.cpu_count() or 1
-    os.environ.setdefault("OMP_NUM_THREADS", str(cores))
+    os.environ["OMP_NUM_THREADS"] = str(cores)      # torchrun exports OMP_NUM_THREADS=1
     if RefTvl1.available():
         impl, kind = RefTvl1(), "reference"
+        RefTvl1.set_threads(cores)
         run = lambda a, b: impl.flow(a, b, nscales=NSCALES)
     else:
         impl, kind = OracleTvl1(), "port"
@@ -91,9 +92,10 @@ def cpu_baseline(seconds_budget=25.0):
     """Reference CPU path on this box's host cores, bounded sample (rank 0, N=1)."""
     from oracle.tvl1 import OracleTvl1, RefTvl1
     cores = os.cpu_count() or 1
-    os.environ.setdefault("OMP_NUM_THREADS", str(cores))
+    os.environ["OMP_NUM_THREADS"] = str(cores)      # torchrun exports OMP_NUM_THREADS=1
     if RefTvl1.available():
         impl, kind = RefTvl1(), "reference"
+        RefTvl1.set_threads(cores)
         run = lambda a, b: impl.flow(a, b, nscales=NSCALES)
     else:
         impl, kind = OracleTvl1(), "port"

@@ -142,6 +142,18 @@ class RefTvl1:
         self.lib = C.CDLL(self.path)
         self.lib.bicubic_interpolation_at.restype = C.c_float
 
+    @staticmethod
+    def set_threads(n):
+        """main.c:143-146: omp_set_num_threads(nproc).  Explicit, because a launcher (torchrun) may have exported
+        OMP_NUM_THREADS=1 before this process started."""
+        for name in ("libgomp.so.1", "libgomp.so"):
+            try:
+                C.CDLL(name).omp_set_num_threads(int(n))
+                return True
+            except OSError:
+                continue
+        return False
+
     def flow(self, I0, I1, tau=0.25, lam=0.15, theta=0.3, nscales=100, fscale=0,
              zfactor=0.5, nwarps=5, epsilon=0.01, clamp=True):
         I0 = np.array(I0, np.float32, order="C")
