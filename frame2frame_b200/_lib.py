@@ -55,6 +55,8 @@ def _declare(lib):
     lib.f2f_dncnn_set_trace.restype = None
     lib.f2f_dncnn_set_legacy.argtypes = [C.c_int]
     lib.f2f_dncnn_set_legacy.restype = None
+    lib.f2f_set_pdl.argtypes = [C.c_int]
+    lib.f2f_set_pdl.restype = None
     lib.f2f_dncnn_forward.argtypes = [fp, fp, vp, fp, fp, vp, sz, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp]
     lib.f2f_dncnn_backward.argtypes = [fp, fp, fp, vp, sz, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp]
     lib.f2f_adam_step.argtypes = [fp, fp, fp, fp, sz, C.c_longlong, C.c_float, C.c_float, C.c_float, C.c_float,

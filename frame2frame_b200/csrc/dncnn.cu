@@ -69,6 +69,8 @@ void prof_end(int cls, cudaStream_t st)
     p.used += 2;
 }
 
+int g_pdl = getenv("F2F_PDL") ? atoi(getenv("F2F_PDL")) : 3;   // programmatic dependent launch, see f2f_common.cuh
+
 namespace dn {
 
 using namespace tc05;
@@ -111,6 +113,7 @@ struct ConvArgs {
     const float *p_invstd;
     int H, W, tiles_x, tiles_y;
     unsigned long long *trace;   // f2f_dncnn_set_trace: per-role cycle counters (development aid) or NULL
+    int pdl_trigger;             // release the dependent launch early (f2f_common.cuh)
 };
 
 unsigned long long *g_conv_trace = nullptr;
@@ -585,6 +588,8 @@ k_conv64t(ConvArgs a, const __grid_constant__ CUtensorMap tm_in, const __grid_co
     __syncthreads();
     fence_after_sync();
     const uint32_t tmem_base = *tmem_ptr;
+    pdl_wait();                  // everything above ran under the predecessor's tail (f2f_common.cuh)
+    if (a.pdl_trigger) pdl_launch_dependents();
 
     if (warp == TMA_A_WARP) {
         // ===== operand tiles: one tensor load per tile (18 rows x 10 pixels x 128 B, zero fill outside) =====
@@ -843,7 +848,9 @@ static int launch_conv64t(ConvArgs a, cudaStream_t st)
     const int ntiles = a.tiles_x * a.tiles_y;
     const int grid = ntiles < sms ? ntiles : sms;
     prof_begin(0, st);
-    k_conv64t<PRO, EPI><<<grid, PRO == dn::PRO_BN_RELU ? NTHREADS_BN : NTHREADS_RAW, SMEM_BYTES, st>>>(a, tm_in, tm_z);
+    a.pdl_trigger = (g_pdl >> 2) & 1;
+    F2F_CUDA_CHECK(launch_pdl(1, k_conv64t<PRO, EPI>, dim3(grid), dim3(PRO == dn::PRO_BN_RELU ? NTHREADS_BN : NTHREADS_RAW),
+                              SMEM_BYTES, st, a, tm_in, tm_z));
     prof_end(0, st);
     g_dncnn_launches++;
     F2F_LAUNCH_CHECK();
@@ -920,6 +927,7 @@ void f2f_profile_dncnn_read(double out[4])
 }
 
 void f2f_dncnn_set_trace(unsigned long long *d_counters) { g_conv_trace = d_counters; }
+void f2f_set_pdl(int on) { f2f::g_pdl = on; }
 void f2f_dncnn_set_legacy(int on) { g_conv_legacy = on != 0; }
 
 int f2f_dncnn_prep_w64(const float *d_w, void *d_wprep, int transpose, void *stream)

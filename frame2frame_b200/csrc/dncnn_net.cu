@@ -58,8 +58,10 @@ __global__ void k_prep_all(const float *__restrict__ params, bf16 *__restrict__ 
 // with the unbiased variance, num_batches_tracked.
 __global__ void k_bn_finalize(const double *__restrict__ stats, const float *__restrict__ gamma,
                               const float *__restrict__ beta, float *__restrict__ running, long long *nbt,
-                              float *__restrict__ coef, double n)
+                              float *__restrict__ coef, double n, int trig)
 {
+    if (trig) pdl_launch_dependents();     // the next convolution sets itself up while this finishes (f2f_common.cuh)
+    pdl_wait();
     const int c = threadIdx.x;
     if (c >= 64) return;
     const double mean = stats[c] / n;
@@ -100,8 +102,10 @@ __global__ void k_bn_eval_coeffs(const float *__restrict__ params, const float *
 // layer's weight gradient.
 __global__ void k_bn_bwd_coeffs(const double *__restrict__ stats, const float *__restrict__ gamma,
                                 float *__restrict__ coef, float *__restrict__ dgamma, float *__restrict__ dbeta,
-                                double n, int accumulate)
+                                double n, int accumulate, int trig)
 {
+    if (trig) pdl_launch_dependents();
+    pdl_wait();
     const int c = threadIdx.x;
     if (c >= 64) return;
     const double db = stats[c], dg = stats[64 + c];
@@ -469,6 +473,7 @@ struct Args {
     const float *coef;     // A, B, C of layer k
     float *partial;        // [gridDim.x][PARTIAL]
     int H, W, tiles_x, tiles_y;
+    int pdl_trigger;
 };
 
 __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a)
@@ -497,6 +502,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a)
     __syncthreads();
     fence_after_sync();
     const uint32_t tmem_base = *tmem_ptr;
+    pdl_wait();                  // set-up above overlapped the predecessor's tail (f2f_common.cuh)
+    if (a.pdl_trigger) pdl_launch_dependents();
 
     // role of this warp: producer warp index pw in 0..7 of group grp, or the MMA warp
     const int grp = warp > MMA_WARP ? 1 : 0;
@@ -668,8 +675,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a)
 
 // dW[oc][ic][ky][kx] (+)= sum over CTA partials.  tap (ky,kx): ky < 2 -> accumulator kx, rows
 // ky*64 + ic; ky == 2 -> accumulator 3 + kx, rows ic.
-__global__ void k_wgrad_reduce(const float *__restrict__ partial, int nparts, float *__restrict__ dw, int accumulate)
+__global__ void k_wgrad_reduce(const float *__restrict__ partial, int nparts, float *__restrict__ dw, int accumulate, int trig)
 {
+    if (trig) pdl_launch_dependents();
+    pdl_wait();
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= 9 * 4096) return;
     const int oc = idx & 63, ic = (idx >> 6) & 63, tap = idx >> 12;
@@ -801,9 +810,10 @@ int f2f_dncnn_forward(const float *d_params, float *d_bn_running, long long *d_n
             if (rc) return rc;
         }
         if (train) {
-            k_bn_finalize<<<1, 64, 0, st>>>(stats_f + (size_t)(k - 1) * 128, d_params + off_gamma(k), d_params + off_beta(k),
-                                            d_bn_running + (size_t)(k - 1) * 128, d_nbt ? d_nbt + (k - 1) : nullptr,
-                                            coef + (size_t)(k - 1) * C_STRIDE, (double)B * (double)P);
+            F2F_CUDA_CHECK(launch_pdl(0, k_bn_finalize, dim3(1), dim3(64), 0, st, stats_f + (size_t)(k - 1) * 128,
+                                      d_params + off_gamma(k), d_params + off_beta(k), d_bn_running + (size_t)(k - 1) * 128,
+                                      d_nbt ? d_nbt + (k - 1) : nullptr, coef + (size_t)(k - 1) * C_STRIDE,
+                                      (double)B * (double)P, (g_pdl >> 3) & 1));
             g_dncnn_launches++;
         }
     }
@@ -837,9 +847,11 @@ int f2f_dncnn_wgrad64(const void *d_act, const float *d_coef_in, void *d_g, cons
     const int ntiles = a.tiles_x * a.tiles_y;
     const int grid = ntiles < num_sms() ? ntiles : num_sms();
     prof_begin(1, st);
-    wg::k_wgrad64<<<grid, wg::NTHREADS, wg::SMEM_BYTES, st>>>(a);
+    a.pdl_trigger = (g_pdl >> 2) & 1;
+    F2F_CUDA_CHECK(launch_pdl(1, wg::k_wgrad64, dim3(grid), dim3(wg::NTHREADS), wg::SMEM_BYTES, st, a));
     prof_end(1, st);
-    wg::k_wgrad_reduce<<<cdiv(9 * 4096, 256), 256, 0, st>>>(d_partial, grid, d_dw, accumulate);
+    F2F_CUDA_CHECK(launch_pdl(0, wg::k_wgrad_reduce, dim3(cdiv(9 * 4096, 256)), dim3(256), 0, st, (const float *)d_partial, grid,
+                              d_dw, accumulate, (g_pdl >> 3) & 1));
     g_dncnn_launches += 2;
     F2F_LAUNCH_CHECK();
     return F2F_OK;
@@ -895,8 +907,8 @@ int f2f_dncnn_backward(const float *d_params, float *d_grads, const float *d_dy,
     for (int k = NBN; k >= 1; k--) {
         dump(2 * (k - 1), gbuf[cur]);
         float *cf = coef + (size_t)(k - 1) * C_STRIDE;
-        k_bn_bwd_coeffs<<<1, 64, 0, st>>>(stats_b + (size_t)(k - 1) * 128, d_params + off_gamma(k), cf,
-                                          d_grads + off_gamma(k), d_grads + off_beta(k), n, accumulate);
+        F2F_CUDA_CHECK(launch_pdl(0, k_bn_bwd_coeffs, dim3(1), dim3(64), 0, st, (const double *)(stats_b + (size_t)(k - 1) * 128),
+                                  d_params + off_gamma(k), cf, d_grads + off_gamma(k), d_grads + off_beta(k), n, accumulate, (g_pdl >> 3) & 1));
         g_dncnn_launches++;
         const bf16 *act = k == 1 ? a0 : zbuf(k - 1);
         const float *cf_in = k == 1 ? nullptr : coef + (size_t)(k - 2) * C_STRIDE;

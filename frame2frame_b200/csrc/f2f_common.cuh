@@ -26,10 +26,35 @@ void set_error(const char *fmt, ...);
 void prof_begin(int cls, cudaStream_t st);
 void prof_end(int cls, cudaStream_t st);
 
+// Programmatic dependent launch (PDL).  Kernels of the per-layer DnCNN chain (64->64 convolution, input gradient, weight
+// gradient and the small BatchNorm / reduction kernels between them) are launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization: the successor's launch is processed while the predecessor still
+// runs, its CTAs are scheduled as SMs free up, and they block in pdl_wait() until the predecessor grid has completed
+// and flushed.  Every kernel launched this way MUST execute pdl_wait() before touching global memory, which makes the
+// ordering transitive along the chain.  g_pdl is a bit mask (f2f_set_pdl / F2F_PDL in the environment): bit 0 the
+// attribute on the big kernels, bit 1 on the small ones, bit 2 an early pdl_launch_dependents() in the big kernels,
+// bit 3 in the small ones.  Measured at 1080p on one box (train iteration, profiles/r01_pdl_ab.log): 0 (fully
+// serialised) 9.03 ms, 3 (default: attributes only) 8.69 ms, 11 8.69 ms, 15 (all early triggers) 9.28 ms -- releasing
+// the dependents early from a persistent kernel that owns every SM only parks their CTAs, so it is off.
+extern int g_pdl;   // bit 0: attribute on the big kernels, 1: on the small ones, 2: early trigger in the big, 3: in the small
+template <class... KArgs, class... Args>
+static inline cudaError_t launch_pdl(int big, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = (g_pdl >> (big ? 0 : 1)) & 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 #ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ float warp_sum(float v)
 {
 #pragma unroll

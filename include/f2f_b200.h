@@ -220,6 +220,10 @@ void f2f_dncnn_set_trace(unsigned long long *d_counters);
 /* Development aid: on != 0 routes the BN+ReLU-prologue convolutions to the older register-staged
  * kernel (dn::k_conv64) instead of the TMA-fed one with in-place transform warps, for comparison. */
 void f2f_dncnn_set_legacy(int on);
+/* Programmatic dependent launch of the per-layer DnCNN kernel chain: bit mask, default 3 (launch attribute on the big
+ * and the small kernels, no early trigger); 0 launches the same kernels fully serialised (F2F_PDL in the environment
+ * sets the initial value).  Results are identical, only the gaps between kernels differ (csrc/f2f_common.cuh). */
+void f2f_set_pdl(int on);
 int f2f_dncnn_forward(const float *d_params, float *d_bn_running, long long *d_nbt,
                       const float *d_x, float *d_y, void *d_ws, size_t ws_bytes, int B, int H,
                       int W, int train, int residual, void *stream);
