@@ -13,6 +13,7 @@
 //   conv0.weight[64][1][3][3] | for k = 1..15: conv_k.weight[64][64][3][3], bn_k.weight[64],
 //   bn_k.bias[64] | conv16.weight[1][64][3][3]
 #include <cuda_bf16.h>
+#include <stdlib.h>
 #include "f2f_common.cuh"
 #include "tc05.cuh"
 
@@ -474,6 +475,7 @@ struct Args {
     float *partial;        // [gridDim.x][PARTIAL]
     int H, W, tiles_x, tiles_y;
     int pdl_trigger;
+    int m64;               // taps ky = 2 as M = 64 instructions (F2F_WGRAD_M64)
 };
 
 __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a)
@@ -572,8 +574,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a)
                     uint32_t r[32];
                     tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + j * 64 + part * 32, r);
                     tmem_ld_wait();
-                    if (j < 3 || row < 64) {
-                        float4 *o = reinterpret_cast<float4 *>(dst + ((size_t)j * 128 + row) * 64 + part * 32);
+                    // M = 64 accumulators (a.m64, taps ky = 2): row i of D sits in TMEM lane 32 * (i / 16) + i % 16
+                    const bool m64 = a.m64 && j >= 3;
+                    const int orow = m64 ? warp * 16 + lane : row;
+                    if (m64 ? lane < 16 : (j < 3 || row < 64)) {
+                        float4 *o = reinterpret_cast<float4 *>(dst + ((size_t)j * 128 + orow) * 64 + part * 32);
 #pragma unroll
                         for (int q = 0; q < 8; q++)
                             o[q] = make_float4(__uint_as_float(r[4 * q]), __uint_as_float(r[4 * q + 1]),
@@ -641,6 +646,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a)
         // ===== MMA issuer: converged warp, the elected lane issues (see dncnn.cu) =====
         const uint32_t el = elect_one();
         constexpr uint32_t IDESC = idesc_bf16(128, 64, 1, 1);
+        // the third vertical tap has no partner row: as an M = 64 instruction it reads 2 KB of A instead of 4 KB
+        constexpr uint32_t IDESC64 = idesc_bf16(64, 64, 1, 1);
         // descriptors differ only in the start-address field (low word, 16-byte units)
         const uint64_t ad0 = smem_desc(0, 128, A_S), bd0 = smem_desc(0, 128, D_S);
         const uint32_t a_hi = (uint32_t)(ad0 >> 32), b_hi = (uint32_t)(bd0 >> 32);
@@ -659,7 +666,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a)
                 for (int j = 0; j < 6; j++) {
                     const int dy = j < 3 ? 0 : 2, dx = j % 3;
                     const uint64_t ad = ((uint64_t)a_hi << 32) | (a_lo + (r + dy) * (A_R / 16) + dx);
-                    mma_ss_el(tmem_base + j * 64, ad, bd, IDESC, (it | r) != 0, el);
+                    mma_ss_el(tmem_base + j * 64, ad, bd, (j >= 3 && a.m64) ? IDESC64 : IDESC, (it | r) != 0, el);
                 }
             }
             if (el) mma_commit(BAR(STAGES + s));
@@ -848,6 +855,8 @@ int f2f_dncnn_wgrad64(const void *d_act, const float *d_coef_in, void *d_g, cons
     const int grid = ntiles < num_sms() ? ntiles : num_sms();
     prof_begin(1, st);
     a.pdl_trigger = (g_pdl >> 2) & 1;
+    static const int m64 = getenv("F2F_WGRAD_M64") ? atoi(getenv("F2F_WGRAD_M64")) : 1;   // 0: M = 128 throughout (A/B, profiles/r01_m64_ab.log)
+    a.m64 = m64;
     F2F_CUDA_CHECK(launch_pdl(1, wg::k_wgrad64, dim3(grid), dim3(wg::NTHREADS), wg::SMEM_BYTES, st, a));
     prof_end(1, st);
     F2F_CUDA_CHECK(launch_pdl(0, wg::k_wgrad_reduce, dim3(cdiv(9 * 4096, 256)), dim3(256), 0, st, (const float *)d_partial, grid,
