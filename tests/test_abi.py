@@ -56,3 +56,32 @@ def test_flo_roundtrip_matches_reference_layout(tmp_path):
     back = read_flo(path)
     assert back.shape == (3, 5, 2)
     assert np.array_equal(back.transpose(2, 0, 1), flow)
+
+
+def test_product_package_never_imports_the_oracle():
+    """oracle/ is the checker: nothing under frame2frame_b200/ may import or execute it (no CPU fallback)."""
+    import os
+    import re
+    pkg = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "frame2frame_b200")
+    bad = []
+    for root, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith(".py"):
+                text = open(os.path.join(root, f)).read()
+                if re.search(r"^\s*(from|import)\s+oracle\b", text, flags=re.M) or "oracle/_ref" in text or "liboracle" in text:
+                    bad.append(os.path.join(root, f))
+    assert not bad, bad
+
+
+def test_tvl1flow_cli_positionals_follow_main_c():
+    """main.c:25-35,86-99: 13 positionals, the same defaults; a missing image pair is a usage error."""
+    import pytest
+    from frame2frame_b200 import tvl1flow_cli
+    v = tvl1flow_cli.parse_positionals(["a.png", "b.png"])
+    assert (v["out"], v["nproc"], v["tau"], v["lam"], v["theta"], v["nscales"], v["fscale"], v["zfactor"], v["nwarps"],
+            v["epsilon"], v["verbose"]) == ("flow.flo", 4, 0.25, 0.15, 0.3, 100, 0, 0.5, 5, 0.01, 0)
+    v = tvl1flow_cli.parse_positionals("a b out.flo 8 0.2 0.1 0.4 5 1 0.6 3 0.02 1".split())
+    assert (v["out"], v["nproc"], v["tau"], v["lam"], v["theta"], v["nscales"], v["fscale"], v["zfactor"], v["nwarps"],
+            v["epsilon"], v["verbose"]) == ("out.flo", 8, 0.2, 0.1, 0.4, 5, 1, 0.6, 3, 0.02, 1)
+    with pytest.raises(SystemExit):
+        tvl1flow_cli.parse_positionals(["only_one.png"])
