@@ -57,6 +57,7 @@ def _declare(lib):
     lib.f2f_dncnn_set_legacy.restype = None
     lib.f2f_set_pdl.argtypes = [C.c_int]
     lib.f2f_set_pdl.restype = None
+    lib.f2f_dncnn_storage_dtype.restype = C.c_int
     lib.f2f_dncnn_forward.argtypes = [fp, fp, vp, fp, fp, vp, sz, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp]
     lib.f2f_dncnn_backward.argtypes = [fp, fp, fp, vp, sz, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp]
     lib.f2f_adam_step.argtypes = [fp, fp, fp, fp, sz, C.c_longlong, C.c_float, C.c_float, C.c_float, C.c_float,
@@ -85,6 +86,12 @@ def lib():
         _lib = C.CDLL(LIB_PATH)
         _declare(_lib)
     return _lib
+
+
+def storage_dtype():
+    """torch dtype of the DnCNN activation / operand buffers the library was built with (f2f_dncnn_storage_dtype)."""
+    import torch
+    return torch.float16 if lib().f2f_dncnn_storage_dtype() else torch.bfloat16
 
 
 def check(rc, what):

@@ -74,7 +74,7 @@ int g_pdl = getenv("F2F_PDL") ? atoi(getenv("F2F_PDL")) : 3;   // programmatic d
 namespace dn {
 
 using namespace tc05;
-typedef __nv_bfloat16 bf16;
+typedef tc05::h16 h16;
 
 constexpr int TW = 16, TH = 16;              // output tile
 constexpr int HW = TW + 2, HH = TH + 2;      // with the 1-px halo of a 3x3 filter
@@ -100,13 +100,13 @@ enum Prologue { PRO_RAW = 0, PRO_BN_RELU = 1 };
 enum Epilogue { EPI_STORE = 0, EPI_STATS = 1, EPI_DGRAD_BN = 2, EPI_DGRAD_RELU = 3 };
 
 struct ConvArgs {
-    const bf16 *in;        // [H][W][64]
-    bf16 *out;             // [H][W][64]
-    const bf16 *wprep;     // [9 taps][8 k-chunks][64 n][8 k] BF16 = the smem image of B
+    const h16 *in;        // [H][W][64]
+    h16 *out;             // [H][W][64]
+    const h16 *wprep;     // [9 taps][8 k-chunks][64 n][8 k] BF16 = the smem image of B
     const float *scale;    // prologue BN: a = relu(in*scale + shift), per input channel
     const float *shift;
     double *stats;         // [2][64] accumulators (EPI_STATS: sum z, sum z^2; EPI_DGRAD_BN: sum g, sum g*xhat)
-    const bf16 *zprev;     // EPI_DGRAD_*: pre-activation (BN) or activation (RELU) of the layer below
+    const h16 *zprev;     // EPI_DGRAD_*: pre-activation (BN) or activation (RELU) of the layer below
     const float *p_scale;  // EPI_DGRAD_BN: BN of the layer below: y = z*p_scale + p_shift, xhat = (z - p_mean)*p_invstd
     const float *p_shift;
     const float *p_mean;
@@ -158,10 +158,10 @@ __device__ __forceinline__ void produce_tile(const ConvArgs &a, int tile, uint8_
                 uint32_t w[4] = {o.x, o.y, o.z, o.w};
 #pragma unroll
                 for (int j = 0; j < 4; j++) {
-                    const float2 f = unpack_bf16(w[j]);
+                    const float2 f = unpack_h16(w[j]);
                     const float y0 = fmaxf(fmaf(f.x, sc[2 * j], sh[2 * j]), 0.0f);
                     const float y1 = fmaxf(fmaf(f.y, sc[2 * j + 1], sh[2 * j + 1]), 0.0f);
-                    w[j] = pack_bf16(y0, y1);
+                    w[j] = pack_h16(y0, y1);
                 }
                 o = make_uint4(w[0], w[1], w[2], w[3]);
             }
@@ -207,10 +207,10 @@ __device__ __forceinline__ void epilogue_half(const ConvArgs &a, uint32_t tmem_a
 #pragma unroll
         for (int j = 0; j < 4; j++) {
             uint4 o;
-            o.x = pack_bf16(__uint_as_float(r[8 * j + 0]), __uint_as_float(r[8 * j + 1]));
-            o.y = pack_bf16(__uint_as_float(r[8 * j + 2]), __uint_as_float(r[8 * j + 3]));
-            o.z = pack_bf16(__uint_as_float(r[8 * j + 4]), __uint_as_float(r[8 * j + 5]));
-            o.w = pack_bf16(__uint_as_float(r[8 * j + 6]), __uint_as_float(r[8 * j + 7]));
+            o.x = pack_h16(__uint_as_float(r[8 * j + 0]), __uint_as_float(r[8 * j + 1]));
+            o.y = pack_h16(__uint_as_float(r[8 * j + 2]), __uint_as_float(r[8 * j + 3]));
+            o.z = pack_h16(__uint_as_float(r[8 * j + 4]), __uint_as_float(r[8 * j + 5]));
+            o.w = pack_h16(__uint_as_float(r[8 * j + 6]), __uint_as_float(r[8 * j + 7]));
             *reinterpret_cast<uint4 *>(myrow + part * 64 + j * 16) = o;
         }
     }
@@ -228,8 +228,8 @@ __device__ __forceinline__ void epilogue_half(const ConvArgs &a, uint32_t tmem_a
             const uint32_t zw[4] = {zz[i].x, zz[i].y, zz[i].z, zz[i].w};
 #pragma unroll
             for (int j = 0; j < 4; j++) {
-                float2 g = unpack_bf16(w[j]);
-                const float2 z = unpack_bf16(zw[j]);
+                float2 g = unpack_h16(w[j]);
+                const float2 z = unpack_h16(zw[j]);
                 if (EPI == EPI_DGRAD_BN) {
                     if (!(fmaf(z.x, cf.sc[2 * j], cf.sh[2 * j]) > 0.0f)) g.x = 0.0f;
                     if (!(fmaf(z.y, cf.sc[2 * j + 1], cf.sh[2 * j + 1]) > 0.0f)) g.y = 0.0f;
@@ -242,14 +242,14 @@ __device__ __forceinline__ void epilogue_half(const ConvArgs &a, uint32_t tmem_a
                     if (!(z.x > 0.0f)) g.x = 0.0f;
                     if (!(z.y > 0.0f)) g.y = 0.0f;
                 }
-                w[j] = pack_bf16(g.x, g.y);
+                w[j] = pack_h16(g.x, g.y);
             }
             o = make_uint4(w[0], w[1], w[2], w[3]);
         }
         if (EPI == EPI_STATS && inb) {
 #pragma unroll
             for (int j = 0; j < 4; j++) {
-                const float2 v = unpack_bf16(w[j]);
+                const float2 v = unpack_h16(w[j]);
                 acc0[2 * j] += v.x; acc0[2 * j + 1] += v.y;
                 acc1[2 * j] = fmaf(v.x, v.x, acc1[2 * j]); acc1[2 * j + 1] = fmaf(v.y, v.y, acc1[2 * j + 1]);
             }
@@ -321,7 +321,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv64(ConvArgs a)
         }
         __syncwarp();
         mbar_wait(BAR(10), 0);
-        constexpr uint32_t IDESC = idesc_bf16(128, 64, 0, 0);
+        constexpr uint32_t IDESC = idesc_h16(128, 64, 0, 0);
         // descriptors differ only in the start-address field (low word, 16-byte units)
         const uint64_t bd0 = smem_desc(smem_u32(smem + OFF_B), 1024, 128);
         const uint32_t b_lo = (uint32_t)bd0, b_hi = (uint32_t)(bd0 >> 32);
@@ -458,7 +458,7 @@ using dn::EPI_STORE;
 using dn::EPI_STATS;
 using dn::EPI_DGRAD_BN;
 using dn::EPI_DGRAD_RELU;
-typedef __nv_bfloat16 bf16;
+typedef tc05::h16 h16;
 
 constexpr int TW = 8, TH = 16;
 constexpr int HW = TW + 2, HH = TH + 2, HPIX = HW * HH;   // 10 x 18 = 180 pixels
@@ -503,10 +503,10 @@ __device__ __forceinline__ void epilogue_tile(const ConvArgs &a, uint32_t tmem_a
 #pragma unroll
         for (int j = 0; j < 4; j++) {
             uint4 o;
-            o.x = pack_bf16(__uint_as_float(r[8 * j + 0]), __uint_as_float(r[8 * j + 1]));
-            o.y = pack_bf16(__uint_as_float(r[8 * j + 2]), __uint_as_float(r[8 * j + 3]));
-            o.z = pack_bf16(__uint_as_float(r[8 * j + 4]), __uint_as_float(r[8 * j + 5]));
-            o.w = pack_bf16(__uint_as_float(r[8 * j + 6]), __uint_as_float(r[8 * j + 7]));
+            o.x = pack_h16(__uint_as_float(r[8 * j + 0]), __uint_as_float(r[8 * j + 1]));
+            o.y = pack_h16(__uint_as_float(r[8 * j + 2]), __uint_as_float(r[8 * j + 3]));
+            o.z = pack_h16(__uint_as_float(r[8 * j + 4]), __uint_as_float(r[8 * j + 5]));
+            o.w = pack_h16(__uint_as_float(r[8 * j + 6]), __uint_as_float(r[8 * j + 7]));
             *reinterpret_cast<uint4 *>(myrow + part * 64 + j * 16) = o;
         }
     }
@@ -526,8 +526,8 @@ __device__ __forceinline__ void epilogue_tile(const ConvArgs &a, uint32_t tmem_a
             const uint32_t zw[4] = {zv.x, zv.y, zv.z, zv.w};
 #pragma unroll
             for (int j = 0; j < 4; j++) {
-                float2 g = unpack_bf16(w[j]);
-                const float2 z = unpack_bf16(zw[j]);
+                float2 g = unpack_h16(w[j]);
+                const float2 z = unpack_h16(zw[j]);
                 if (EPI == EPI_DGRAD_BN) {
                     if (!(fmaf(z.x, cf.sc[2 * j], cf.sh[2 * j]) > 0.0f)) g.x = 0.0f;
                     if (!(fmaf(z.y, cf.sc[2 * j + 1], cf.sh[2 * j + 1]) > 0.0f)) g.y = 0.0f;
@@ -540,14 +540,14 @@ __device__ __forceinline__ void epilogue_tile(const ConvArgs &a, uint32_t tmem_a
                     if (!(z.x > 0.0f)) g.x = 0.0f;
                     if (!(z.y > 0.0f)) g.y = 0.0f;
                 }
-                w[j] = pack_bf16(g.x, g.y);
+                w[j] = pack_h16(g.x, g.y);
             }
             o = make_uint4(w[0], w[1], w[2], w[3]);
         }
         if (EPI == EPI_STATS && inb) {
 #pragma unroll
             for (int j = 0; j < 4; j++) {
-                const float2 v = unpack_bf16(w[j]);
+                const float2 v = unpack_h16(w[j]);
                 acc0[2 * j] += v.x; acc0[2 * j + 1] += v.y;
                 acc1[2 * j] = fmaf(v.x, v.x, acc1[2 * j]); acc1[2 * j + 1] = fmaf(v.y, v.y, acc1[2 * j + 1]);
             }
@@ -657,8 +657,8 @@ k_conv64t(ConvArgs a, const __grid_constant__ CUtensorMap tm_in, const __grid_co
                     uint32_t w[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
 #pragma unroll
                     for (int j = 0; j < 4; j++) {
-                        const float2 f = unpack_bf16(w[j]);
-                        w[j] = pack_bf16(fmaxf(fmaf(f.x, sc[2 * j], sh[2 * j]), 0.0f),
+                        const float2 f = unpack_h16(w[j]);
+                        w[j] = pack_h16(fmaxf(fmaf(f.x, sc[2 * j], sh[2 * j]), 0.0f),
                                          fmaxf(fmaf(f.y, sc[2 * j + 1], sh[2 * j + 1]), 0.0f));
                     }
                     *reinterpret_cast<uint4 *>(st + pix * 128 + ((chunk ^ (pix & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
@@ -676,7 +676,7 @@ k_conv64t(ConvArgs a, const __grid_constant__ CUtensorMap tm_in, const __grid_co
         }
         __syncwarp();
         mbar_wait(BAR(B_W), 0);
-        constexpr uint32_t IDESC = idesc_bf16(128, 64, 0, 0);
+        constexpr uint32_t IDESC = idesc_h16(128, 64, 0, 0);
         const uint64_t bd0 = smem_desc(smem_u32(smem + OFF_B), 1024, 128);
         const uint32_t b_lo = (uint32_t)bd0, b_hi = (uint32_t)(bd0 >> 32);
         const uint64_t ad0 = smem_desc_sw128(0, HW * 128);
@@ -816,7 +816,7 @@ static int make_tensor_map(CUtensorMap *m, const void *base, int H, int W, int b
         }
         encode = (encode_fn)fn;
     }
-    const CUresult r = encode(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void *>(base), dims, strides, box,
+    const CUresult r = encode(m, (tc05::H16_FORMAT ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16), 3, const_cast<void *>(base), dims, strides, box,
                               estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
@@ -864,7 +864,7 @@ namespace dn {
 //   forward (transpose = 0): B_tap[n = oc][k = ic] = w[oc][ic][tap]
 //   dgrad   (transpose = 1): B_tap[n = ic][k = oc] = w[oc][ic][8 - tap]   (flipped filter, transposed channels)
 // image order: [tap][k chunk of 8][n][8 k] bf16.
-__global__ void k_prep_w64(const float *__restrict__ w, bf16 *__restrict__ out, int transpose)
+__global__ void k_prep_w64(const float *__restrict__ w, h16 *__restrict__ out, int transpose)
 {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= 9 * 64 * 64) return;
@@ -873,7 +873,7 @@ __global__ void k_prep_w64(const float *__restrict__ w, bf16 *__restrict__ out, 
     float v;
     if (!transpose) v = w[((size_t)n * 64 + k) * 9 + tap];
     else v = w[((size_t)k * 64 + n) * 9 + (8 - tap)];
-    out[idx] = __float2bfloat16(v);
+    out[idx] = tc05::float_to_h16(v);
 }
 
 template <int PRO, int EPI>
@@ -928,12 +928,13 @@ void f2f_profile_dncnn_read(double out[4])
 
 void f2f_dncnn_set_trace(unsigned long long *d_counters) { g_conv_trace = d_counters; }
 void f2f_set_pdl(int on) { f2f::g_pdl = on; }
+int f2f_dncnn_storage_dtype(void) { return tc05::H16_FORMAT ? 0 : 1; }
 void f2f_dncnn_set_legacy(int on) { g_conv_legacy = on != 0; }
 
 int f2f_dncnn_prep_w64(const float *d_w, void *d_wprep, int transpose, void *stream)
 {
     if (!d_w || !d_wprep) { set_error("f2f_dncnn_prep_w64: bad arguments"); return F2F_EINVAL; }
-    k_prep_w64<<<cdiv(9 * 64 * 64, 256), 256, 0, (cudaStream_t)stream>>>(d_w, (bf16 *)d_wprep, transpose);
+    k_prep_w64<<<cdiv(9 * 64 * 64, 256), 256, 0, (cudaStream_t)stream>>>(d_w, (h16 *)d_wprep, transpose);
     g_dncnn_launches++;
     F2F_LAUNCH_CHECK();
     return F2F_OK;
@@ -944,7 +945,7 @@ int f2f_dncnn_conv64(const void *d_in, void *d_out, const void *d_wprep, const f
 {
     if (!d_in || !d_out || !d_wprep || H < 1 || W < 1) { set_error("f2f_dncnn_conv64: bad arguments"); return F2F_EINVAL; }
     ConvArgs a = {};
-    a.in = (const bf16 *)d_in; a.out = (bf16 *)d_out; a.wprep = (const bf16 *)d_wprep;
+    a.in = (const h16 *)d_in; a.out = (h16 *)d_out; a.wprep = (const h16 *)d_wprep;
     a.scale = d_scale; a.shift = d_shift; a.stats = d_stats;
     a.H = H; a.W = W; a.tiles_x = cdiv(W, TW); a.tiles_y = cdiv(H, TH);
     a.trace = g_conv_trace;
@@ -966,8 +967,8 @@ int f2f_dncnn_dgrad64(const void *d_dz, void *d_gout, const void *d_wprep_t, con
 {
     if (!d_dz || !d_gout || !d_wprep_t || !d_zprev || H < 1 || W < 1) { set_error("f2f_dncnn_dgrad64: bad arguments"); return F2F_EINVAL; }
     ConvArgs a = {};
-    a.in = (const bf16 *)d_dz; a.out = (bf16 *)d_gout; a.wprep = (const bf16 *)d_wprep_t;
-    a.zprev = (const bf16 *)d_zprev; a.p_scale = d_pscale; a.p_shift = d_pshift; a.p_mean = d_pmean; a.p_invstd = d_pinvstd;
+    a.in = (const h16 *)d_dz; a.out = (h16 *)d_gout; a.wprep = (const h16 *)d_wprep_t;
+    a.zprev = (const h16 *)d_zprev; a.p_scale = d_pscale; a.p_shift = d_pshift; a.p_mean = d_pmean; a.p_invstd = d_pinvstd;
     a.stats = d_stats;
     a.H = H; a.W = W; a.tiles_x = cdiv(W, TW); a.tiles_y = cdiv(H, TH);
     a.trace = g_conv_trace;

@@ -22,7 +22,7 @@ extern long g_dncnn_launches;
 namespace net {
 
 using namespace tc05;
-typedef __nv_bfloat16 bf16;
+typedef tc05::h16 h16;
 
 constexpr int NBN = 15;
 constexpr int WSZ = 64 * 64 * 9;                   // 36864
@@ -41,7 +41,7 @@ enum { C_SCALE = 0, C_SHIFT = 64, C_MEAN = 128, C_INVSTD = 192, C_A = 256, C_B =
 
 // all 30 tensor-core operand images (15 forward, 15 transposed/flipped) in one launch; same
 // element mapping as k_prep_w64 in dncnn.cu
-__global__ void k_prep_all(const float *__restrict__ params, bf16 *__restrict__ wprep)
+__global__ void k_prep_all(const float *__restrict__ params, h16 *__restrict__ wprep)
 {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= 30 * WSZ) return;
@@ -51,7 +51,7 @@ __global__ void k_prep_all(const float *__restrict__ params, bf16 *__restrict__ 
     const int kk = e & 7, n = (e >> 3) & 63, kc = (e >> 9) & 7, tap = e >> 12;
     const int kch = kc * 8 + kk;
     const float v = !transpose ? w[((size_t)n * 64 + kch) * 9 + tap] : w[((size_t)kch * 64 + n) * 9 + (8 - tap)];
-    wprep[idx] = __float2bfloat16(v);
+    wprep[idx] = tc05::float_to_h16(v);
 }
 
 // Train-mode BatchNorm2d bookkeeping of one layer: batch mean / biased variance from
@@ -162,7 +162,7 @@ constexpr int OFF_X = 2 * ZSTAGE, OFF_BAR = OFF_X + ((XH * XW * 4 + 15) & ~15);
 constexpr int SMEM = OFF_BAR + 16;
 
 // thread 0: rows of tile (ty0, tx0) of `img` -> stage at `dst`, completion on `bar`
-__device__ __forceinline__ void stage_tile(uint32_t dst, uint32_t bar, const bf16 *img, int ty0, int tx0, int H, int W)
+__device__ __forceinline__ void stage_tile(uint32_t dst, uint32_t bar, const h16 *img, int ty0, int tx0, int H, int W)
 {
     const int rows = min(TH, H - ty0), nx = min(TW, W - tx0);
     fence_proxy_async();                                  // the stage was last read through the generic proxy
@@ -199,9 +199,9 @@ __device__ __forceinline__ void block_pair_reduce(const float (&v)[NV], float *s
 // Backward of the last layer: input gradient (1->64 transposed conv) masked by layer 15's ReLU, its
 // BatchNorm-backward sums, and the last layer's weight gradient -- one pass over z15.
 //   g15[q][ic]  = relu'(.) * sum_k dn[q - k + 1] * w16[ic][k]        dW16[ic][k] = sum_q a15[q][ic] * dn[q - k + 1]
-__global__ void __launch_bounds__(NT, 1) k_last_bwd(const float *__restrict__ dy, float dy_sign, const bf16 *__restrict__ z,
+__global__ void __launch_bounds__(NT, 1) k_last_bwd(const float *__restrict__ dy, float dy_sign, const h16 *__restrict__ z,
                                                     const float *__restrict__ coef, const float *__restrict__ w16,
-                                                    bf16 *__restrict__ g, double *__restrict__ stats,
+                                                    h16 *__restrict__ g, double *__restrict__ stats,
                                                     double *__restrict__ dw16, int H, int W, int tiles_x, int ntiles)
 {
     extern __shared__ __align__(128) uint8_t smem[];
@@ -235,11 +235,11 @@ __global__ void __launch_bounds__(NT, 1) k_last_bwd(const float *__restrict__ dy
         const int y = ty0 + r, nx = min(TW, W - tx0);
         if (y < H) {
             const uint8_t *zrow = smem + s * ZSTAGE + r * ZROW + lane * 4;
-            bf16 *grow = g + ((size_t)y * W + tx0) * 64 + c0;
+            h16 *grow = g + ((size_t)y * W + tx0) * 64 + c0;
             const float *d2 = dnS + (r + 2) * XW + 2;       // dn[ky][kx] at d2[-ky * XW - kx + x]
 #pragma unroll 4
             for (int x = xh; x < min(xh + 32, nx); x++) {
-                const float2 zz = unpack_bf16(*reinterpret_cast<const uint32_t *>(zrow + x * 128));
+                const float2 zz = unpack_h16(*reinterpret_cast<const uint32_t *>(zrow + x * 128));
                 const float y0 = fmaf(zz.x, sc[0], sh[0]), y1 = fmaf(zz.y, sc[1], sh[1]);
                 const float a0 = fmaxf(y0, 0.0f), a1 = fmaxf(y1, 0.0f);
                 float s0 = 0.0f, s1 = 0.0f;
@@ -249,9 +249,9 @@ __global__ void __launch_bounds__(NT, 1) k_last_bwd(const float *__restrict__ dy
                     s0 = fmaf(dn, w[t][0], s0); s1 = fmaf(dn, w[t][1], s1);
                     acc[2 * t] = fmaf(a0, dn, acc[2 * t]); acc[2 * t + 1] = fmaf(a1, dn, acc[2 * t + 1]);
                 }
-                const uint32_t o = pack_bf16(y0 > 0.0f ? s0 : 0.0f, y1 > 0.0f ? s1 : 0.0f);
+                const uint32_t o = pack_h16(y0 > 0.0f ? s0 : 0.0f, y1 > 0.0f ? s1 : 0.0f);
                 *reinterpret_cast<uint32_t *>(grow + (size_t)x * 64) = o;
-                const float2 gr = unpack_bf16(o);             // sums of the ROUNDED gradient, like the tcgen05 epilogue
+                const float2 gr = unpack_h16(o);             // sums of the ROUNDED gradient, like the tcgen05 epilogue
                 acc[18] += gr.x; acc[19] += gr.y;
                 acc[20] = fmaf(gr.x, fmaf(zz.x, is[0], ms[0]), acc[20]);
                 acc[21] = fmaf(gr.y, fmaf(zz.y, is[1], ms[1]), acc[21]);
@@ -267,7 +267,7 @@ __global__ void __launch_bounds__(NT, 1) k_last_bwd(const float *__restrict__ dy
 }
 
 // Weight gradient of the first layer: dW0[oc][k] = sum_p g0[p][oc] * x[p + k - 1]
-__global__ void __launch_bounds__(NT, 1) k_first_wgrad(const bf16 *__restrict__ g0, const float *__restrict__ x,
+__global__ void __launch_bounds__(NT, 1) k_first_wgrad(const h16 *__restrict__ g0, const float *__restrict__ x,
                                                        double *__restrict__ dw0, int H, int W, int tiles_x, int ntiles)
 {
     extern __shared__ __align__(128) uint8_t smem[];
@@ -296,7 +296,7 @@ __global__ void __launch_bounds__(NT, 1) k_first_wgrad(const bf16 *__restrict__ 
             const float *x0 = xS + r * XW;                   // x[p + (ky-1, kx-1)] at x0[ky * XW + kx + x]
 #pragma unroll 4
             for (int x_ = xh; x_ < min(xh + 32, nx); x_++) {
-                const float2 gg = unpack_bf16(*reinterpret_cast<const uint32_t *>(grow + x_ * 128));
+                const float2 gg = unpack_h16(*reinterpret_cast<const uint32_t *>(grow + x_ * 128));
 #pragma unroll
                 for (int t = 0; t < 9; t++) {
                     const float xv = x0[x_ + (t / 3) * XW + (t % 3)];
@@ -312,7 +312,7 @@ __global__ void __launch_bounds__(NT, 1) k_first_wgrad(const bf16 *__restrict__ 
 
 // Conv(1->64, 3x3, pad 1) + ReLU (net.py:13-14): FP32 image -> NHWC BF16 activation; a warp writes one pixel's 128 bytes per step.
 constexpr int FT = 256;                              // 8 warps: warp = tile row
-__global__ void __launch_bounds__(FT) k_first_fwd(const float *__restrict__ x, const float *__restrict__ w0, bf16 *__restrict__ a0,
+__global__ void __launch_bounds__(FT) k_first_fwd(const float *__restrict__ x, const float *__restrict__ w0, h16 *__restrict__ a0,
                                                   int H, int W, int tiles_x, int ntiles)
 {
     __shared__ float xS[XH * XW];
@@ -333,7 +333,7 @@ __global__ void __launch_bounds__(FT) k_first_fwd(const float *__restrict__ x, c
         const int y = ty0 + r, nx = min(TW, W - tx0);
         if (y >= H) continue;
         const float *x0 = xS + r * XW;
-        bf16 *orow = a0 + ((size_t)y * W + tx0) * 64 + c0;
+        h16 *orow = a0 + ((size_t)y * W + tx0) * 64 + c0;
 #pragma unroll 4
         for (int x_ = 0; x_ < nx; x_++) {
             float s0 = 0.0f, s1 = 0.0f;
@@ -342,7 +342,7 @@ __global__ void __launch_bounds__(FT) k_first_fwd(const float *__restrict__ x, c
                 const float xv = x0[x_ + (t / 3) * XW + (t % 3)];
                 s0 = fmaf(xv, w[t][0], s0); s1 = fmaf(xv, w[t][1], s1);
             }
-            *reinterpret_cast<uint32_t *>(orow + (size_t)x_ * 64) = pack_bf16(fmaxf(s0, 0.0f), fmaxf(s1, 0.0f));
+            *reinterpret_cast<uint32_t *>(orow + (size_t)x_ * 64) = pack_h16(fmaxf(s0, 0.0f), fmaxf(s1, 0.0f));
         }
     }
 }
@@ -352,7 +352,7 @@ __global__ void __launch_bounds__(FT) k_first_fwd(const float *__restrict__ x, c
 // haloed 18x18 tile: the lane reads its pixel's 128 bytes (eight 16-byte loads in flight), forms the nine per-tap
 // dot products over all 64 channels with no cross-lane reduction (weights and coefficients are warp-uniform
 // shared-memory reads), and the output pixel sums nine shifted partials from shared memory.
-__global__ void __launch_bounds__(256) k_last_fwd(const bf16 *__restrict__ z, const float *__restrict__ coef,
+__global__ void __launch_bounds__(256) k_last_fwd(const h16 *__restrict__ z, const float *__restrict__ coef,
                                                   const float *__restrict__ w16, const float *__restrict__ x,
                                                   float *__restrict__ out, int H, int W, int tiles_x, int ntiles, int residual)
 {
@@ -388,7 +388,7 @@ __global__ void __launch_bounds__(256) k_last_fwd(const bf16 *__restrict__ z, co
                     float a[8];
 #pragma unroll
                     for (int q = 0; q < 4; q++) {
-                        const float2 f = unpack_bf16(vw[q]);
+                        const float2 f = unpack_h16(vw[q]);
                         a[2 * q] = fmaxf(fmaf(f.x, scv[2 * q], shv[2 * q]), 0.0f);
                         a[2 * q + 1] = fmaxf(fmaf(f.y, scv[2 * q + 1], shv[2 * q + 1]), 0.0f);
                     }
@@ -467,10 +467,10 @@ constexpr int PARTIAL = 6 * 128 * 64;   // floats per CTA
 constexpr int HPIX = HR * 18, DPIX = TR * 16;
 
 struct Args {
-    const bf16 *act;       // layer input: z_{k-1} (BN+ReLU applied on load) or a_0 (raw)
+    const h16 *act;       // layer input: z_{k-1} (BN+ReLU applied on load) or a_0 (raw)
     const float *coef_in;  // scale/shift of layer k-1, or NULL
-    bf16 *g;               // in: masked gradient g_k; out: dz_k
-    const bf16 *z;         // pre-BN output z_k
+    h16 *g;               // in: masked gradient g_k; out: dz_k
+    const h16 *z;         // pre-BN output z_k
     const float *coef;     // A, B, C of layer k
     float *partial;        // [gridDim.x][PARTIAL]
     int H, W, tiles_x, tiles_y;
@@ -549,8 +549,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a)
                         uint32_t w[4] = {o.x, o.y, o.z, o.w};
 #pragma unroll
                         for (int j = 0; j < 4; j++) {
-                            const float2 f = unpack_bf16(w[j]);
-                            w[j] = pack_bf16(fmaxf(fmaf(f.x, sc[2 * j], sh[2 * j]), 0.0f),
+                            const float2 f = unpack_h16(w[j]);
+                            w[j] = pack_h16(fmaxf(fmaf(f.x, sc[2 * j], sh[2 * j]), 0.0f),
                                              fmaxf(fmaf(f.y, sc[2 * j + 1], sh[2 * j + 1]), 0.0f));
                         }
                         o = make_uint4(w[0], w[1], w[2], w[3]);
@@ -628,8 +628,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a)
                     uint32_t w[4];
 #pragma unroll
                     for (int j = 0; j < 4; j++) {
-                        const float2 gg = unpack_bf16(gw[j]), zz = unpack_bf16(zw[j]);
-                        w[j] = pack_bf16(fmaf(cA[2 * j], gg.x, fmaf(cB[2 * j], zz.x, cC[2 * j])),
+                        const float2 gg = unpack_h16(gw[j]), zz = unpack_h16(zw[j]);
+                        w[j] = pack_h16(fmaf(cA[2 * j], gg.x, fmaf(cB[2 * j], zz.x, cC[2 * j])),
                                          fmaf(cA[2 * j + 1], gg.y, fmaf(cB[2 * j + 1], zz.y, cC[2 * j + 1])));
                     }
                     o = make_uint4(w[0], w[1], w[2], w[3]);
@@ -645,9 +645,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a)
     } else {
         // ===== MMA issuer: converged warp, the elected lane issues (see dncnn.cu) =====
         const uint32_t el = elect_one();
-        constexpr uint32_t IDESC = idesc_bf16(128, 64, 1, 1);
+        constexpr uint32_t IDESC = idesc_h16(128, 64, 1, 1);
         // the third vertical tap has no partner row: as an M = 64 instruction it reads 2 KB of A instead of 4 KB
-        constexpr uint32_t IDESC64 = idesc_bf16(64, 64, 1, 1);
+        constexpr uint32_t IDESC64 = idesc_h16(64, 64, 1, 1);
         // descriptors differ only in the start-address field (low word, 16-byte units)
         const uint64_t ad0 = smem_desc(0, 128, A_S), bd0 = smem_desc(0, 128, D_S);
         const uint32_t a_hi = (uint32_t)(ad0 >> 32), b_hi = (uint32_t)(bd0 >> 32);
@@ -785,11 +785,11 @@ int f2f_dncnn_forward(const float *d_params, float *d_bn_running, long long *d_n
     cudaStream_t st = (cudaStream_t)stream;
     uint8_t *ws = (uint8_t *)d_ws;
     const size_t P = (size_t)H * W;
-    bf16 *wprep = (bf16 *)(ws + pl.o_wprep);
+    h16 *wprep = (h16 *)(ws + pl.o_wprep);
     float *coef = (float *)(ws + pl.o_coef);
     double *stats_f = (double *)(ws + pl.o_stats_f);
-    bf16 *a0 = (bf16 *)(ws + pl.o_a0);
-    auto zbuf = [&](int k) { return (bf16 *)(ws + pl.o_z + pl.act_bytes * (size_t)(train ? k - 1 : (k & 1))); };
+    h16 *a0 = (h16 *)(ws + pl.o_a0);
+    auto zbuf = [&](int k) { return (h16 *)(ws + pl.o_z + pl.act_bytes * (size_t)(train ? k - 1 : (k & 1))); };
 
     k_prep_all<<<cdiv(30 * WSZ, 256), 256, 0, st>>>(d_params, wprep);
     g_dncnn_launches++;
@@ -808,7 +808,7 @@ int f2f_dncnn_forward(const float *d_params, float *d_bn_running, long long *d_n
     }
     F2F_LAUNCH_CHECK();
     for (int k = 1; k <= NBN; k++) {
-        const bf16 *in = k == 1 ? a0 : zbuf(k - 1);
+        const h16 *in = k == 1 ? a0 : zbuf(k - 1);
         const float *cf = k == 1 ? nullptr : coef + (size_t)(k - 2) * C_STRIDE;
         for (int b = 0; b < B; b++) {
             const int rc = f2f_dncnn_conv64(in + b * P * 64, zbuf(k) + b * P * 64, wprep + (size_t)(k - 1) * WSZ,
@@ -849,7 +849,7 @@ int f2f_dncnn_wgrad64(const void *d_act, const float *d_coef_in, void *d_g, cons
     }
     cudaStream_t st = (cudaStream_t)stream;
     wg::Args a;
-    a.act = (const bf16 *)d_act; a.coef_in = d_coef_in; a.g = (bf16 *)d_g; a.z = (const bf16 *)d_z; a.coef = d_coef;
+    a.act = (const h16 *)d_act; a.coef_in = d_coef_in; a.g = (h16 *)d_g; a.z = (const h16 *)d_z; a.coef = d_coef;
     a.partial = d_partial; a.H = H; a.W = W; a.tiles_x = cdiv(W, 16); a.tiles_y = cdiv(H, wg::TR);
     const int ntiles = a.tiles_x * a.tiles_y;
     const int grid = ntiles < num_sms() ? ntiles : num_sms();
@@ -888,15 +888,15 @@ int f2f_dncnn_backward(const float *d_params, float *d_grads, const float *d_dy,
     uint8_t *ws = (uint8_t *)d_ws;
     const size_t P = (size_t)H * W;
     const double n = (double)B * (double)P;
-    const bf16 *wprep = (const bf16 *)(ws + pl.o_wprep);
+    const h16 *wprep = (const h16 *)(ws + pl.o_wprep);
     float *coef = (float *)(ws + pl.o_coef);
     double *stats_b = (double *)(ws + pl.o_stats_b);
     double *dw0 = (double *)(ws + pl.o_dw_small), *dw16 = dw0 + 576;
     const float *x = (const float *)(ws + pl.o_x);
-    bf16 *a0 = (bf16 *)(ws + pl.o_a0);
+    h16 *a0 = (h16 *)(ws + pl.o_a0);
     float *partial = (float *)(ws + pl.o_partial);
-    auto zbuf = [&](int k) { return (bf16 *)(ws + pl.o_z + pl.act_bytes * (size_t)(k - 1)); };
-    bf16 *gbuf[2] = {(bf16 *)(ws + pl.o_g0), (bf16 *)(ws + pl.o_g1)};
+    auto zbuf = [&](int k) { return (h16 *)(ws + pl.o_z + pl.act_bytes * (size_t)(k - 1)); };
+    h16 *gbuf[2] = {(h16 *)(ws + pl.o_g0), (h16 *)(ws + pl.o_g1)};
 
     // stats_b and the small double accumulators are adjacent (make_plan)
     F2F_CUDA_CHECK(cudaMemsetAsync(stats_b, 0, (pl.o_dw_small - pl.o_stats_b) + 1152 * 8, st));
@@ -919,7 +919,7 @@ int f2f_dncnn_backward(const float *d_params, float *d_grads, const float *d_dy,
         F2F_CUDA_CHECK(launch_pdl(0, k_bn_bwd_coeffs, dim3(1), dim3(64), 0, st, (const double *)(stats_b + (size_t)(k - 1) * 128),
                                   d_params + off_gamma(k), cf, d_grads + off_gamma(k), d_grads + off_beta(k), n, accumulate, (g_pdl >> 3) & 1));
         g_dncnn_launches++;
-        const bf16 *act = k == 1 ? a0 : zbuf(k - 1);
+        const h16 *act = k == 1 ? a0 : zbuf(k - 1);
         const float *cf_in = k == 1 ? nullptr : coef + (size_t)(k - 2) * C_STRIDE;
         for (int b = 0; b < B; b++) {
             int rc = f2f_dncnn_wgrad64(act + b * P * 64, cf_in, gbuf[cur] + b * P * 64, zbuf(k) + b * P * 64, cf, partial,

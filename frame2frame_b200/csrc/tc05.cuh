@@ -4,6 +4,7 @@
 // (checked against cute/arch/mma_sm100_desc.hpp of the vendored CUTLASS tree).
 #pragma once
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -127,12 +128,23 @@ __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t addr, uint32_t sbo_
            (1ull << 46) | (2ull << 61);
 }
 
-// Instruction descriptor for kind::f16, BF16 x BF16 -> F32:
-//   c_format F32 = 1 @ bit 4, a_format BF16 = 1 @ bit 7, b_format BF16 = 1 @ bit 10,
+// 16-bit storage type of the DnCNN activations, gradients and tensor-core operands.  kind::f16 takes FP16 and BF16
+// at the same rate; BF16 (8-bit mantissa, FP32's range) is the default, -DF2F_STORE_FP16 selects FP16 (11-bit
+// mantissa; the values here -- BatchNorm-normalised activations, sum-loss gradients, weights ~0.05 -- fit its range).
+#ifdef F2F_STORE_FP16
+typedef __half h16;
+constexpr uint32_t H16_FORMAT = 0;     // idesc a_format / b_format: 0 = F16
+#else
+typedef __nv_bfloat16 h16;
+constexpr uint32_t H16_FORMAT = 1;     // 1 = BF16
+#endif
+
+// Instruction descriptor for kind::f16, 16-bit x 16-bit -> F32:
+//   c_format F32 = 1 @ bit 4, a_format @ bit 7, b_format @ bit 10 (0 = F16, 1 = BF16),
 //   a_major @ bit 15, b_major @ bit 16 (0 = K-major, 1 = MN-major), N>>3 @ bit 17, M>>4 @ bit 24.
-__host__ __device__ constexpr uint32_t idesc_bf16(int M, int N, int a_mn_major, int b_mn_major)
+__host__ __device__ constexpr uint32_t idesc_h16(int M, int N, int a_mn_major, int b_mn_major)
 {
-    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) |
+    return (1u << 4) | (H16_FORMAT << 7) | (H16_FORMAT << 10) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) |
            ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
@@ -178,14 +190,28 @@ __device__ __forceinline__ bool elect_one()
     return pred != 0;
 }
 
-__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi)
+#ifdef F2F_STORE_FP16
+__device__ __forceinline__ uint32_t pack_h16(float lo, float hi)
+{
+    __half2 v = __floats2half2_rn(lo, hi);
+    return *reinterpret_cast<uint32_t *>(&v);
+}
+__device__ __forceinline__ float2 unpack_h16(uint32_t v)
+{
+    return __half22float2(*reinterpret_cast<const __half2 *>(&v));
+}
+__device__ __forceinline__ h16 float_to_h16(float v) { return __float2half_rn(v); }
+#else
+__device__ __forceinline__ uint32_t pack_h16(float lo, float hi)
 {
     __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
     return *reinterpret_cast<uint32_t *>(&v);
 }
-__device__ __forceinline__ float2 unpack_bf16(uint32_t v)
+__device__ __forceinline__ float2 unpack_h16(uint32_t v)
 {
     return make_float2(__uint_as_float(v << 16), __uint_as_float(v & 0xffff0000u));
 }
+__device__ __forceinline__ h16 float_to_h16(float v) { return __float2bfloat16(v); }
+#endif
 
 }  // namespace tc05

@@ -16,8 +16,11 @@ import torch.nn.functional as F
 EPS = 1e-5
 
 
+STORAGE = torch.bfloat16     # the CUDA path's 16-bit storage type (tests set it from f2f_dncnn_storage_dtype)
+
+
 def bf(t):
-    return t.to(torch.bfloat16).to(torch.float32)
+    return t.to(STORAGE).to(torch.float32)
 
 
 # Which classes of tensors are rounded to BF16 (all of them = the CUDA path's data flow).  The

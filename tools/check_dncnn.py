@@ -17,6 +17,8 @@ torch.backends.cudnn.allow_tf32 = False
 torch.backends.cuda.matmul.allow_tf32 = False
 dev = torch.device("cuda:0")
 lib = _lib.lib()
+H16 = _lib.storage_dtype()      # BF16 or FP16, whatever the library was built with
+emu.STORAGE = H16
 ok = True
 
 
@@ -33,9 +35,9 @@ def check_wgrad(H, W):
     """k_wgrad64 alone vs torch: dW = conv2d_weight(a, dz)"""
     global ok
     torch.manual_seed(1)
-    z_prev = torch.randn(1, 64, H, W, device=dev).bfloat16()
-    g = (torch.randn(1, 64, H, W, device=dev) * 0.1).bfloat16()
-    z = torch.randn(1, 64, H, W, device=dev).bfloat16()
+    z_prev = torch.randn(1, 64, H, W, device=dev).to(H16)
+    g = (torch.randn(1, 64, H, W, device=dev) * 0.1).to(H16)
+    z = torch.randn(1, 64, H, W, device=dev).to(H16)
     coef_in = torch.zeros(448, device=dev)
     coef_in[0:64] = torch.rand(64, device=dev) + 0.5
     coef_in[64:128] = torch.randn(64, device=dev) * 0.3
@@ -56,9 +58,9 @@ def check_wgrad(H, W):
         torch.cuda.synchronize()
         a = z_prev.float()
         if bn_in:
-            a = torch.relu(a * coef_in[0:64].view(1, -1, 1, 1) + coef_in[64:128].view(1, -1, 1, 1)).bfloat16().float()
+            a = torch.relu(a * coef_in[0:64].view(1, -1, 1, 1) + coef_in[64:128].view(1, -1, 1, 1)).to(H16).float()
         dz = (coef[256:320].view(1, -1, 1, 1) * g.float() + coef[320:384].view(1, -1, 1, 1) * z.float()
-              + coef[384:448].view(1, -1, 1, 1)).bfloat16()
+              + coef[384:448].view(1, -1, 1, 1)).to(H16)
         ref = torch.nn.grad.conv2d_weight(a, (64, 64, 3, 3), dz.float(), padding=1)
         e_dw = rel(dw, ref)
         e_dz = float((g_nhwc.permute(0, 3, 1, 2).float() - dz.float()).abs().max())
@@ -150,7 +152,7 @@ def check_layers(H, W, seed=0):
     lay = (C.c_size_t * 8)()
     lib.f2f_dncnn_workspace_layout(1, H, W, 1, lay)
     buf = net._ws_train.buf
-    act = lambda off: buf[off:off + H * W * 128].view(torch.bfloat16).view(1, H, W, 64).permute(0, 3, 1, 2).float()
+    act = lambda off: buf[off:off + H * W * 128].view(H16).view(1, H, W, 64).permute(0, 3, 1, 2).float()
     coef = buf[lay[6]:lay[6] + 15 * 448 * 4].view(torch.float32).view(15, 448)
     w0, mid, w16 = emu.unpack(net.flat_params.detach())
     a0 = act(lay[1])
@@ -205,7 +207,7 @@ def check_backward_layers(H, W, seed=0):
     torch.cuda.synchronize()
     lib.f2f_dncnn_set_debug_dump(None)
     buf = net._ws_train.buf
-    nhwc = lambda t, off: t[off:off + H * W * 128].view(torch.bfloat16).view(1, H, W, 64).permute(0, 3, 1, 2).float()
+    nhwc = lambda t, off: t[off:off + H * W * 128].view(H16).view(1, H, W, 64).permute(0, 3, 1, 2).float()
     coef = buf[lay[6]:lay[6] + 15 * 448 * 4].view(torch.float32).view(15, 448)
     w0, mid, w16 = emu.unpack(net.flat_params.detach())
     gw0, gmid, gw16 = emu.unpack(net.flat_grads.detach())

@@ -4,6 +4,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch, numpy as np
 from frame2frame_b200 import _lib
 lib = _lib.lib()
+H16 = _lib.storage_dtype()
 torch.backends.cudnn.allow_tf32 = False
 torch.backends.cuda.matmul.allow_tf32 = False
 dev = torch.device("cuda:0")
@@ -12,11 +13,11 @@ torch.manual_seed(0)
 def run(H, W, bn, stats):
     x = torch.randn(1, 64, H, W, device=dev)
     w = torch.randn(64, 64, 3, 3, device=dev) * 0.06
-    xb = x.bfloat16()
+    xb = x.to(H16)
     x_nhwc = xb.permute(0, 2, 3, 1).contiguous()           # [1,H,W,64] bf16
-    wprep = torch.empty(9 * 64 * 64, dtype=torch.bfloat16, device=dev)
+    wprep = torch.empty(9 * 64 * 64, dtype=H16, device=dev)
     _lib.check(lib.f2f_dncnn_prep_w64(w.data_ptr(), wprep.data_ptr(), 0, None), "prep")
-    out = torch.full((1, H, W, 64), float("nan"), dtype=torch.bfloat16, device=dev)
+    out = torch.full((1, H, W, 64), float("nan"), dtype=H16, device=dev)
     scale = (torch.rand(64, device=dev) + 0.5) if bn else None
     shift = (torch.randn(64, device=dev) * 0.3) if bn else None
     st = torch.zeros(128, dtype=torch.float64, device=dev) if stats else None
@@ -26,8 +27,8 @@ def run(H, W, bn, stats):
     torch.cuda.synchronize()
     a = xb.float()
     if bn:
-        a = torch.relu(a * scale.view(1, -1, 1, 1) + shift.view(1, -1, 1, 1)).bfloat16().float()
-    ref = torch.nn.functional.conv2d(a, w.bfloat16().float(), padding=1)
+        a = torch.relu(a * scale.view(1, -1, 1, 1) + shift.view(1, -1, 1, 1)).to(H16).float()
+    ref = torch.nn.functional.conv2d(a, w.to(H16).float(), padding=1)
     got = out.permute(0, 3, 1, 2).float()
     err = (got - ref).abs().max().item()
     tol = ref.abs().max().item() * 2 ** -7
@@ -47,9 +48,9 @@ for (H, W) in [(16, 16), (32, 48), (40, 72), (270, 480)]:
             ok &= run(H, W, bn, stats)
 # timing at 1080p
 H, W = 1080, 1920
-x = torch.randn(1, H, W, 64, device=dev).bfloat16()
+x = torch.randn(1, H, W, 64, device=dev).to(H16)
 w = torch.randn(64, 64, 3, 3, device=dev) * 0.06
-wprep = torch.empty(9 * 64 * 64, dtype=torch.bfloat16, device=dev)
+wprep = torch.empty(9 * 64 * 64, dtype=H16, device=dev)
 lib.f2f_dncnn_prep_w64(w.data_ptr(), wprep.data_ptr(), 0, None)
 out = torch.empty_like(x)
 scale = torch.ones(64, device=dev); shift = torch.zeros(64, device=dev)

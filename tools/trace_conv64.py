@@ -4,14 +4,15 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from frame2frame_b200 import _lib
 lib = _lib.lib()
+H16 = _lib.storage_dtype()
 dev = torch.device("cuda:0")
 H, W = (int(sys.argv[1]), int(sys.argv[2])) if len(sys.argv) > 2 else (1080, 1920)
 torch.manual_seed(0)
-x = torch.randn(1, H, W, 64, device=dev).bfloat16()
-z = torch.randn(1, H, W, 64, device=dev).bfloat16()
+x = torch.randn(1, H, W, 64, device=dev).to(H16)
+z = torch.randn(1, H, W, 64, device=dev).to(H16)
 out = torch.empty_like(x)
 w = torch.randn(64, 64, 3, 3, device=dev) * 0.06
-wprep = torch.empty(9 * 64 * 64, dtype=torch.bfloat16, device=dev)
+wprep = torch.empty(9 * 64 * 64, dtype=H16, device=dev)
 lib.f2f_dncnn_prep_w64(w.data_ptr(), wprep.data_ptr(), 0, None)
 ones = torch.ones(64, device=dev); zeros = torch.zeros(64, device=dev)
 st = torch.zeros(128, dtype=torch.float64, device=dev)

@@ -62,7 +62,7 @@ __global__ void __launch_bounds__(128, 1) k_bench(int mode, int reps, float *out
     const uint32_t tmem = *tmem_ptr;
     if (threadIdx.x < 32) {
         const uint32_t el = elect_one();
-        const uint32_t IDESC = idesc_bf16(128, N, 0, 0);
+        const uint32_t IDESC = idesc_h16(128, N, 0, 0);
         const uint32_t a_base = smem_u32(A), b_base = smem_u32(B);
         // descriptors: only the low word (start address >> 4) changes between MMAs
         uint64_t a0, b0;
@@ -203,7 +203,7 @@ __global__ void __launch_bounds__(128, 1) k_issue(int reps, long long *cycles)
     __syncthreads();
     fence_after_sync();
     const uint32_t tmem = *tmem_ptr;
-    constexpr uint32_t IDESC = idesc_bf16(128, 64, 0, 0);
+    constexpr uint32_t IDESC = idesc_h16(128, 64, 0, 0);
     const uint64_t a0 = desc_sw128(smem_u32(smem), HWD * 128, 0), b0 = desc_sw128(smem_u32(smem + A_BYTES), 1024, 0);
     const uint32_t a_lo = (uint32_t)a0, a_hi = (uint32_t)(a0 >> 32), b_lo = (uint32_t)b0, b_hi = (uint32_t)(b0 >> 32);
     const int warp_u = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);   // provably warp-uniform (CUTLASS canonical_warp_idx_sync)
