@@ -106,6 +106,7 @@ def ours(args, rank, world, local_rank, ClockSampler, peaks):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     lib = _lib.lib()                                   # raises if the CUDA library is missing
+    h16 = "fp16" if lib.f2f_dncnn_storage_dtype() else "bf16"
     gold = os.path.join(os.path.dirname(os.path.abspath(__file__)), "tests", "golden", "dncnn_s25_synth.npz")
     engine = OnlineF2F(load_network(gold, dev))
     nf = 4                                             # distinct noisy frames of this rank's chunk, cycled
@@ -187,13 +188,13 @@ def ours(args, rank, world, local_rank, ClockSampler, peaks):
     line = {
         "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "bf16", "data": "synthetic",
+        "dtype": h16, "data": "synthetic",
         "config": {"workload": "configs[2]: online F2F denoise, 1080p gray sigma=25 synthetic seq, DnCNN-25 layout "
                                "(weights pre-trained on synthetic textures: tests/golden/dncnn_s25_synth.npz), iter=20 per "
                                "frame, TV-L1 backward flows computed on the device inside the timed region (up to %d consecutive "
                                "pairs per batched call); 1 frame per step per GPU, " % LOOKAHEAD +
                                "ranks denoise independent chunks (no collective)",
-                   "frame": "%dx%d" % (W, H), "iter": ITERS, "precision": "BF16 operands/activations, FP32 accumulate, "
+                   "frame": "%dx%d" % (W, H), "iter": ITERS, "precision": h16.upper() + " operands/activations/gradients, FP32 accumulate, "
                    "FP32 master weights, Adam and BatchNorm statistics",
                    "l2": "inputs larger than L2: every layer streams 265 MB activations (4.8 GB workspace per step)"},
         "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": H * W * 4, "d2h_bytes_per_step": H * W * 4,
@@ -239,7 +240,7 @@ def ours_batch(args, rank, world, local_rank, ClockSampler, peaks):
     NSEQ = 8
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
-    _lib.lib()
+    h16 = "fp16" if _lib.lib().f2f_dncnn_storage_dtype() else "bf16"
     gold = os.path.join(os.path.dirname(os.path.abspath(__file__)), "tests", "golden", "dncnn_s25_synth.npz")
     eng = BatchF2F(load_network(gold, dev), NSEQ)
     nf = 3
@@ -284,7 +285,7 @@ def ours_batch(args, rank, world, local_rank, ClockSampler, peaks):
     return {
         "metric": "batch-mode F2F fine-tuned frames/sec @1080p gray", "value": value, "unit": "frames/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_max / args.steps, "higher_is_better": True,
-        "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "scaling": "strong", "vs_baseline": None, "dtype": h16, "data": "synthetic",
         "config": {"workload": "configs[3]: batch-mode F2F fine-tune, 8 sequences x 1080p gray sigma=25, iter=20 per frame, one "
                                "Adam step per inner iteration on the summed loss; sequences sharded over ranks, flat 556032-float "
                                "gradient all-reduced with NCCL, BatchNorm batch statistics all-gathered (ordered EMA)",

@@ -19,8 +19,8 @@ INCLUDE = os.path.join(os.path.dirname(HERE), "include")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC",
           "-I", INCLUDE]
-if os.environ.get("F2F_STORE_FP16", "0") not in ("", "0"):
-    COMMON.append("-DF2F_STORE_FP16")     # FP16 instead of BF16 storage of the DnCNN tensors (csrc/tc05.cuh)
+if os.environ.get("F2F_STORE_BF16", "0") not in ("", "0"):
+    COMMON.append("-DF2F_STORE_BF16")     # BF16 instead of FP16 storage of the DnCNN tensors (csrc/tc05.cuh)
 
 # translation unit -> extra flags
 #  tvl1.cu: -fmad=false, the reference C is built without FMA contraction (-std=c99)

@@ -98,34 +98,66 @@ __global__ void k_bn_eval_coeffs(const float *__restrict__ params, const float *
     cf[C_INVSTD + c] = invstd;
 }
 
+// Gradient scaling.  The backward pass is linear in the incoming gradient dy, and its 16-bit intermediates (masked
+// gradients g_k, dz_k) have FP16's range when the library is built with FP16 storage: a mean-reduced loss at 1080p
+// hands in |dy| ~ 5e-7, below FP16's normal range.  So dy is multiplied by the power of two s that brings max|dy| into
+// [1, 2) on entry (k_last_bwd) and every parameter gradient is multiplied by 1/s on exit (k_wgrad_reduce,
+// k_bn_bwd_coeffs, k_small_grads).  Powers of two are exact: for the reference's sum-reduced L1 loss (|dy| = 1,
+// s = 1) and for BF16 storage nothing changes bit-wise.  absmax holds the bits of max|dy| (non-negative floats
+// order like unsigned integers); 0, subnormal or non-finite -> s = 1.
+__device__ __forceinline__ float grad_scale_from_bits(unsigned b, bool inverse)
+{
+    const unsigned E = b >> 23;
+    if (E == 0 || E >= 250) return 1.0f;
+    return __uint_as_float((inverse ? E : 254u - E) << 23);      // 2^(E-127) or 2^(127-E)
+}
+__device__ __forceinline__ float grad_scale(const unsigned *absmax) { return absmax ? grad_scale_from_bits(*absmax, false) : 1.0f; }
+__device__ __forceinline__ float grad_unscale(const unsigned *absmax) { return absmax ? grad_scale_from_bits(*absmax, true) : 1.0f; }
+
+__global__ void k_absmax(const float *__restrict__ v, size_t n, unsigned *__restrict__ absmax)
+{
+    unsigned m = 0;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const unsigned b = __float_as_uint(fabsf(v[i]));
+        m = b > m ? b : m;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const unsigned t = __shfl_xor_sync(0xffffffffu, m, o);
+        m = t > m ? t : m;
+    }
+    if ((threadIdx.x & 31) == 0 && m) atomicMax(absmax, m);
+}
+
 // BatchNorm backward of one layer from the sums the dgrad epilogue produced (sum g, sum g*xhat):
 // dgamma, dbeta into the gradient vector and dz = A*g + B*z + C for the operand staging of the
 // layer's weight gradient.
 __global__ void k_bn_bwd_coeffs(const double *__restrict__ stats, const float *__restrict__ gamma,
                                 float *__restrict__ coef, float *__restrict__ dgamma, float *__restrict__ dbeta,
-                                double n, int accumulate, int trig)
+                                double n, int accumulate, int trig, const unsigned *__restrict__ absmax)
 {
     if (trig) pdl_launch_dependents();
     pdl_wait();
     const int c = threadIdx.x;
     if (c >= 64) return;
     const double db = stats[c], dg = stats[64 + c];
+    const float uns = grad_unscale(absmax);
     const double invstd = coef[C_INVSTD + c], mean = coef[C_MEAN + c], ga = gamma[c];
     coef[C_A + c] = (float)(ga * invstd);
     coef[C_B + c] = (float)(-ga * invstd * invstd * dg / n);
     coef[C_C + c] = (float)(ga * invstd * (-db / n + mean * invstd * dg / n));
-    dgamma[c] = (accumulate ? dgamma[c] : 0.0f) + (float)dg;
-    dbeta[c] = (accumulate ? dbeta[c] : 0.0f) + (float)db;
+    dgamma[c] = (accumulate ? dgamma[c] : 0.0f) + (float)dg * uns;
+    dbeta[c] = (accumulate ? dbeta[c] : 0.0f) + (float)db * uns;
 }
 
 __global__ void k_small_grads(const double *__restrict__ dw0, const double *__restrict__ dw16, float *__restrict__ grads,
-                              int accumulate)
+                              int accumulate, const unsigned *__restrict__ absmax)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= 1152) return;
     float *dst = i < 576 ? grads + OFF_W0 + i : grads + OFF_W16 + (i - 576);
     const double v = i < 576 ? dw0[i] : dw16[i - 576];
-    *dst = (accumulate ? *dst : 0.0f) + (float)v;
+    *dst = (accumulate ? *dst : 0.0f) + (float)v * grad_unscale(absmax);
 }
 
 // torch.optim.Adam (amsgrad=False, L2 weight decay folded into the gradient), single flat tensor;
@@ -202,9 +234,11 @@ __device__ __forceinline__ void block_pair_reduce(const float (&v)[NV], float *s
 __global__ void __launch_bounds__(NT, 1) k_last_bwd(const float *__restrict__ dy, float dy_sign, const h16 *__restrict__ z,
                                                     const float *__restrict__ coef, const float *__restrict__ w16,
                                                     h16 *__restrict__ g, double *__restrict__ stats,
-                                                    double *__restrict__ dw16, int H, int W, int tiles_x, int ntiles)
+                                                    double *__restrict__ dw16, int H, int W, int tiles_x, int ntiles,
+                                                    const unsigned *__restrict__ absmax)
 {
     extern __shared__ __align__(128) uint8_t smem[];
+    dy_sign *= grad_scale(absmax);
     float *dnS = reinterpret_cast<float *>(smem + OFF_X);
     const uint32_t bar0 = smem_u32(smem + OFF_BAR);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, r = warp >> 1, xh = (warp & 1) * 32, c0 = 2 * lane;
@@ -682,7 +716,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a)
 
 // dW[oc][ic][ky][kx] (+)= sum over CTA partials.  tap (ky,kx): ky < 2 -> accumulator kx, rows
 // ky*64 + ic; ky == 2 -> accumulator 3 + kx, rows ic.
-__global__ void k_wgrad_reduce(const float *__restrict__ partial, int nparts, float *__restrict__ dw, int accumulate, int trig)
+__global__ void k_wgrad_reduce(const float *__restrict__ partial, int nparts, float *__restrict__ dw, int accumulate, int trig,
+                               const unsigned *__restrict__ absmax)
 {
     if (trig) pdl_launch_dependents();
     pdl_wait();
@@ -695,14 +730,14 @@ __global__ void k_wgrad_reduce(const float *__restrict__ partial, int nparts, fl
     float t = 0.0f;
     for (int c = 0; c < nparts; c++) t += src[(size_t)c * PARTIAL];
     float *d = dw + ((size_t)oc * 64 + ic) * 9 + tap;
-    *d = (accumulate ? *d : 0.0f) + t;
+    *d = (accumulate ? *d : 0.0f) + t * grad_unscale(absmax);
 }
 }  // namespace wg
 
 // --------------------------------------------------------------- workspace plan
 struct Plan {
     size_t act_bytes;       // one NHWC BF16 activation of the whole batch
-    size_t o_x, o_a0, o_z, o_g0, o_g1, o_wprep, o_stats_f, o_stats_b, o_dw_small, o_coef, o_partial, total;
+    size_t o_x, o_a0, o_z, o_g0, o_g1, o_wprep, o_stats_f, o_stats_b, o_dw_small, o_absmax, o_coef, o_partial, total;
     int nz;
 };
 
@@ -735,6 +770,7 @@ static Plan make_plan(int B, int H, int W, int train)
     p.o_stats_f = take((size_t)NBN * 128 * 8);
     p.o_stats_b = take((size_t)NBN * 128 * 8);     // contiguous with o_dw_small: one memset
     p.o_dw_small = take((size_t)1152 * 8);
+    p.o_absmax = take(16);                         // bits of max|dy| (gradient scaling); zeroed by the same memset
     p.o_coef = take((size_t)NBN * C_STRIDE * 4);
     p.o_partial = train ? take((size_t)148 * 2 * wg::PARTIAL * 4) : 0;
     p.total = o;
@@ -835,8 +871,17 @@ int f2f_dncnn_forward(const float *d_params, float *d_bn_running, long long *d_n
     return F2F_OK;
 }
 
+static int wgrad64_scaled(const void *d_act, const float *d_coef_in, void *d_g, const void *d_z, const float *d_coef,
+                          float *d_partial, float *d_dw, int H, int W, int accumulate, const unsigned *d_absmax, void *stream);
+
 int f2f_dncnn_wgrad64(const void *d_act, const float *d_coef_in, void *d_g, const void *d_z, const float *d_coef,
                       float *d_partial, float *d_dw, int H, int W, int accumulate, void *stream)
+{
+    return wgrad64_scaled(d_act, d_coef_in, d_g, d_z, d_coef, d_partial, d_dw, H, W, accumulate, nullptr, stream);
+}
+
+static int wgrad64_scaled(const void *d_act, const float *d_coef_in, void *d_g, const void *d_z, const float *d_coef,
+                          float *d_partial, float *d_dw, int H, int W, int accumulate, const unsigned *d_absmax, void *stream)
 {
     if (!d_act || !d_g || !d_z || !d_coef || !d_partial || !d_dw || H < 1 || W < 1) {
         set_error("f2f_dncnn_wgrad64: bad arguments");
@@ -860,7 +905,7 @@ int f2f_dncnn_wgrad64(const void *d_act, const float *d_coef_in, void *d_g, cons
     F2F_CUDA_CHECK(launch_pdl(1, wg::k_wgrad64, dim3(grid), dim3(wg::NTHREADS), wg::SMEM_BYTES, st, a));
     prof_end(1, st);
     F2F_CUDA_CHECK(launch_pdl(0, wg::k_wgrad_reduce, dim3(cdiv(9 * 4096, 256)), dim3(256), 0, st, (const float *)d_partial, grid,
-                              d_dw, accumulate, (g_pdl >> 3) & 1));
+                              d_dw, accumulate, (g_pdl >> 3) & 1, d_absmax));
     g_dncnn_launches += 2;
     F2F_LAUNCH_CHECK();
     return F2F_OK;
@@ -899,13 +944,16 @@ int f2f_dncnn_backward(const float *d_params, float *d_grads, const float *d_dy,
     h16 *gbuf[2] = {(h16 *)(ws + pl.o_g0), (h16 *)(ws + pl.o_g1)};
 
     // stats_b and the small double accumulators are adjacent (make_plan)
-    F2F_CUDA_CHECK(cudaMemsetAsync(stats_b, 0, (pl.o_dw_small - pl.o_stats_b) + 1152 * 8, st));
+    unsigned *absmax = (unsigned *)(ws + pl.o_absmax);
+    F2F_CUDA_CHECK(cudaMemsetAsync(stats_b, 0, (pl.o_absmax - pl.o_stats_b) + 16, st));
+    k_absmax<<<num_sms(), 256, 0, st>>>(d_dy, (size_t)B * P, absmax);      // gradient scaling, see grad_scale()
+    g_dncnn_launches++;
     int cur = 0;   // gbuf[cur] holds g_k
     const int rtx = cdiv(W, rs::TW), rnt = rtx * cdiv(H, rs::TH);
     for (int b = 0; b < B; b++) {
         rs::k_last_bwd<<<rnt < num_sms() ? rnt : num_sms(), rs::NT, rs::SMEM, st>>>(
             d_dy + b * P, residual ? -1.0f : 1.0f, zbuf(NBN) + b * P * 64, coef + (size_t)(NBN - 1) * C_STRIDE,
-            d_params + OFF_W16, gbuf[cur] + b * P * 64, stats_b + (size_t)(NBN - 1) * 128, dw16, H, W, rtx, rnt);
+            d_params + OFF_W16, gbuf[cur] + b * P * 64, stats_b + (size_t)(NBN - 1) * 128, dw16, H, W, rtx, rnt, absmax);
         g_dncnn_launches++;
     }
     F2F_LAUNCH_CHECK();
@@ -917,13 +965,13 @@ int f2f_dncnn_backward(const float *d_params, float *d_grads, const float *d_dy,
         dump(2 * (k - 1), gbuf[cur]);
         float *cf = coef + (size_t)(k - 1) * C_STRIDE;
         F2F_CUDA_CHECK(launch_pdl(0, k_bn_bwd_coeffs, dim3(1), dim3(64), 0, st, (const double *)(stats_b + (size_t)(k - 1) * 128),
-                                  d_params + off_gamma(k), cf, d_grads + off_gamma(k), d_grads + off_beta(k), n, accumulate, (g_pdl >> 3) & 1));
+                                  d_params + off_gamma(k), cf, d_grads + off_gamma(k), d_grads + off_beta(k), n, accumulate, (g_pdl >> 3) & 1, (const unsigned *)absmax));
         g_dncnn_launches++;
         const h16 *act = k == 1 ? a0 : zbuf(k - 1);
         const float *cf_in = k == 1 ? nullptr : coef + (size_t)(k - 2) * C_STRIDE;
         for (int b = 0; b < B; b++) {
-            int rc = f2f_dncnn_wgrad64(act + b * P * 64, cf_in, gbuf[cur] + b * P * 64, zbuf(k) + b * P * 64, cf, partial,
-                                       d_grads + off_conv(k), H, W, accumulate || b > 0, stream);
+            int rc = wgrad64_scaled(act + b * P * 64, cf_in, gbuf[cur] + b * P * 64, zbuf(k) + b * P * 64, cf, partial,
+                                    d_grads + off_conv(k), H, W, accumulate || b > 0, absmax, stream);
             if (rc) return rc;
             if (b == B - 1) dump(2 * (k - 1) + 1, gbuf[cur]);
             // input gradient: g_{k-1} = relu'/BN-sums( conv(dz_k, W_k^T) )
@@ -944,7 +992,7 @@ int f2f_dncnn_backward(const float *d_params, float *d_grads, const float *d_dy,
                                                                                        W, rtx, rnt);
         g_dncnn_launches++;
     }
-    k_small_grads<<<cdiv(1152, 256), 256, 0, st>>>(dw0, dw16, d_grads, accumulate);
+    k_small_grads<<<cdiv(1152, 256), 256, 0, st>>>(dw0, dw16, d_grads, accumulate, absmax);
     g_dncnn_launches++;
     F2F_LAUNCH_CHECK();
     return F2F_OK;

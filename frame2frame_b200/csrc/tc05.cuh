@@ -129,14 +129,18 @@ __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t addr, uint32_t sbo_
 }
 
 // 16-bit storage type of the DnCNN activations, gradients and tensor-core operands.  kind::f16 takes FP16 and BF16
-// at the same rate; BF16 (8-bit mantissa, FP32's range) is the default, -DF2F_STORE_FP16 selects FP16 (11-bit
-// mantissa; the values here -- BatchNorm-normalised activations, sum-loss gradients, weights ~0.05 -- fit its range).
-#ifdef F2F_STORE_FP16
-typedef __half h16;
-constexpr uint32_t H16_FORMAT = 0;     // idesc a_format / b_format: 0 = F16
-#else
+// at the same rate.  FP16 (11-bit mantissa) is the default: over the 9 fine-tuned frames of BASELINE.json configs[0]
+// the online loop's PSNR stays within +0.05 dB of the FP32 oracle on average, where BF16's 8-bit mantissa -- coarser
+// than one Adam step on a typical weight -- lags the optimisation and ends -0.19 dB low
+// (profiles/r01_parity_config0_*.json).  The values here fit FP16's range: BatchNorm-normalised activations, weights
+// ~0.05, and gradients that dncnn_net.cu rescales by a power of two on entry (grad_scale).  -DF2F_STORE_BF16 (build.py:
+// F2F_STORE_BF16=1) selects BF16, 3 % faster (its unpack is a shift).
+#ifdef F2F_STORE_BF16
 typedef __nv_bfloat16 h16;
-constexpr uint32_t H16_FORMAT = 1;     // 1 = BF16
+constexpr uint32_t H16_FORMAT = 1;     // idesc a_format / b_format: 1 = BF16
+#else
+typedef __half h16;
+constexpr uint32_t H16_FORMAT = 0;     // 0 = F16
 #endif
 
 // Instruction descriptor for kind::f16, 16-bit x 16-bit -> F32:
@@ -190,7 +194,7 @@ __device__ __forceinline__ bool elect_one()
     return pred != 0;
 }
 
-#ifdef F2F_STORE_FP16
+#ifndef F2F_STORE_BF16
 __device__ __forceinline__ uint32_t pack_h16(float lo, float hi)
 {
     __half2 v = __floats2half2_rn(lo, hi);

@@ -225,7 +225,7 @@ void f2f_dncnn_set_legacy(int on);
  * sets the initial value).  Results are identical, only the gaps between kernels differ (csrc/f2f_common.cuh). */
 void f2f_set_pdl(int on);
 /* 16-bit storage type the library was built with for DnCNN activations, gradients and tensor-core operands:
- * 0 = BF16 (default), 1 = FP16 (-DF2F_STORE_FP16, frame2frame_b200/build.py F2F_STORE_FP16=1).  Callers that
+ * 1 = FP16 (default), 0 = BF16 (-DF2F_STORE_BF16, frame2frame_b200/build.py F2F_STORE_BF16=1).  Callers that
  * pre-pack operand buffers (f2f_dncnn_conv64 / dgrad64 / wgrad64) must use this type. */
 int f2f_dncnn_storage_dtype(void);
 int f2f_dncnn_forward(const float *d_params, float *d_bn_running, long long *d_nbt,

@@ -218,9 +218,12 @@ def check_backward_layers(H, W, seed=0):
     yk = lambda k: z[k] * coef[k - 1, 0:64].view(1, -1, 1, 1) + coef[k - 1, 64:128].view(1, -1, 1, 1)
     act = lambda k: a0 if k == 0 else (emu.bf(F.relu(yk(k))) if k < 15 else F.relu(yk(k)))
     dn = -dy
+    # the 16-bit intermediates (g_k, dz_k) live in a power-of-two scaled domain: max|dy| * sc in [1, 2)
+    # (dncnn_net.cu grad_scale); parameter gradients come out unscaled
+    sc = 2.0 ** -float(torch.floor(torch.log2(dy.abs().max())))
     e = rel(gw16, torch.nn.grad.conv2d_weight(act(15), w16.shape, dn, padding=1))
     g15 = nhwc(dumpbuf, 28 * lay[3])
-    e2 = rel(g15, emu.bf(torch.nn.grad.conv2d_input(z[15].shape, w16, dn, padding=1) * (yk(15) > 0)))
+    e2 = rel(g15, emu.bf(torch.nn.grad.conv2d_input(z[15].shape, w16, dn * sc, padding=1) * (yk(15) > 0)))
     worst = max(worst, e, e2)
     print("backward layers %dx%d: dW16 rel err %.3g, g15 rel err %.3g" % (H, W, e, e2))
     for k in range(15, 0, -1):
@@ -230,14 +233,14 @@ def check_backward_layers(H, W, seed=0):
         gamma = mid[k - 1][1]
         xhat = (z[k] - mean.view(1, -1, 1, 1)) * invstd.view(1, -1, 1, 1)
         dbeta = g.double().sum((0, 2, 3)); dgamma = (g * xhat).double().sum((0, 2, 3))
-        e_bn = max(rel(gmid[k - 1][1], dgamma), rel(gmid[k - 1][2], dbeta))
+        e_bn = max(rel(gmid[k - 1][1], dgamma / sc), rel(gmid[k - 1][2], dbeta / sc))
         A = (gamma * invstd).double()
         Bc = -A * invstd.double() * dgamma / n_el
         Cc = A * (-dbeta / n_el + mean.double() * invstd.double() * dgamma / n_el)
         e_cf = max(rel(coef[k - 1, 256:320], A), rel(coef[k - 1, 320:384], Bc), rel(coef[k - 1, 384:448], Cc))
         cA, cB, cC = (coef[k - 1, i:i + 64].view(1, -1, 1, 1) for i in (256, 320, 384))
         e_dz = rel(dz, emu.bf(cA * g + (cB * z[k] + cC)))
-        e_dw = rel(gmid[k - 1][0], torch.nn.grad.conv2d_weight(act(k - 1), (64, 64, 3, 3), dz, padding=1))
+        e_dw = rel(gmid[k - 1][0], torch.nn.grad.conv2d_weight(act(k - 1), (64, 64, 3, 3), dz, padding=1) / sc)
         gin = torch.nn.grad.conv2d_input(z[k].shape, emu.bf(mid[k - 1][0]), dz, padding=1)
         mask = (yk(k - 1) > 0) if k >= 2 else (a0 > 0)
         gprev = nhwc(dumpbuf, (2 * (k - 2) if k >= 2 else 30) * lay[3])
@@ -245,7 +248,7 @@ def check_backward_layers(H, W, seed=0):
         worst = max(worst, e_bn, e_cf, e_dz, e_dw, e_g)
         print("   layer %-2d dgamma/dbeta %.3g, A/B/C %.3g, dz %.3g, dW %.3g, g_prev %.3g" % (k, e_bn, e_cf, e_dz, e_dw, e_g))
     g0 = nhwc(dumpbuf, 30 * lay[3])
-    e = rel(gw0, torch.nn.grad.conv2d_weight(x, w0.shape, g0, padding=1))
+    e = rel(gw0, torch.nn.grad.conv2d_weight(x, w0.shape, g0, padding=1) / sc)
     worst = max(worst, e)
     good = worst < 2e-3
     print("   dW0 rel err %.3g -> %s" % (e, "OK" if good else "FAIL"))
