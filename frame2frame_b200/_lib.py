@@ -7,7 +7,8 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "lib", "libf2f_b200.so")
+# F2F_LIB points at another build of the same library (the storage-format variants of build.py, for A/B runs)
+LIB_PATH = os.environ.get("F2F_LIB") or os.path.join(HERE, "lib", "libf2f_b200.so")
 
 _lib = None
 
