@@ -23,6 +23,7 @@ import torch.nn as nn
 
 from ._lib import check, lib
 from .dncnn import Adam, DnCNN
+from .frame_io import OrderedSink, Prefetcher
 from .tvl1 import read_flo, tvl1flow
 from .warped_loss import WarpedLoss, warp_mask
 
@@ -193,24 +194,19 @@ def blind_denoising(**args):
 
     first, last = args["first"], args["last"]
 
-    class _Frames:                       # frame k of the run = file index first + k, read when the loop reaches it
-        def __len__(self):
-            return last - first + 1
+    def read_frame(k):                   # frame k of the run = file index first + k (blind_denoising.py:170-180,192-203)
+        return torch.FloatTensor(_to_batch(imread_gray(args["input"] % (first + k)))).pin_memory()
 
-        def __getitem__(self, k):
-            return torch.FloatTensor(_to_batch(imread_gray(args["input"] % (first + k))))
-
-    class _Flows:                        # --flow files: flow from frame i to frame i-1 (blind_denoising.py:206-209)
-        def __getitem__(self, k):
-            return torch.Tensor(np.expand_dims(read_flo(args["flow"] % (first + k)), 0)).permute(0, 3, 1, 2)
+    def read_flow(k):                    # --flow files: flow from frame i to frame i-1 (blind_denoising.py:206-209)
+        return torch.Tensor(np.expand_dims(read_flo(args["flow"] % (first + k)), 0)).permute(0, 3, 1, 2)
 
     plot_psnr = open(args["output_psnr"], "w")
-    flows = _Flows() if args.get("flow") else None
-    for k, den in engine.run_sequence(_Frames(), iters=args["iter"], lookahead=int(args.get("lookahead", 16) or 1),
-                                      flows=flows):
-        i = first + k
+
+    def finish_frame(i, den_host, ready):
+        """blind_denoising.py:233-253 for frame i, on the writer thread: save, score, log -- in frame order."""
+        ready.synchronize()
         print(i)
-        den_np = np.array(den.cpu())
+        den_np = np.array(den_host)
         if _is_tiff(args["ref"]):
             imsave(args["output"] % (i), np.squeeze(255. * den_np).astype(np.float32))
         else:
@@ -219,6 +215,20 @@ def blind_denoising(**args):
         quant = psnr(ref, den_np)
         plot_psnr.write(str(quant) + "\n")
         print(quant)
+
+    lookahead = int(args.get("lookahead", 16) or 1)
+    n = last - first + 1
+    # decode ahead of the loop and encode/score behind it on host threads (frame_io.py); the loop itself never
+    # waits on a PNG.  Each frame gets its own pinned result buffer, alive until the writer is done with it.
+    with Prefetcher(read_frame, n, depth=lookahead + 2, workers=4) as frames, \
+            Prefetcher(read_flow, n, depth=2, workers=1) as flow_files, OrderedSink(depth=8) as sink:
+        flows = flow_files if args.get("flow") else None
+        for k, den in engine.run_sequence(frames, iters=args["iter"], lookahead=lookahead, flows=flows):
+            host = torch.empty(den.shape, dtype=den.dtype, pin_memory=True)
+            host.copy_(den, non_blocking=True)
+            ready = torch.cuda.Event()
+            ready.record()
+            sink.submit(finish_frame, first + k, host, ready)
     torch.save([model, engine.optimizer], args["output_network"])
     plot_psnr.close()
 
