@@ -69,6 +69,7 @@ void prof_end(int cls, cudaStream_t st)
     p.used += 2;
 }
 
+int g_conv_pair = getenv("F2F_CONV_PAIR") ? atoi(getenv("F2F_CONV_PAIR")) : 0;   // CTA-pair (cta_group::2) convolutions, experimental
 int g_pdl = getenv("F2F_PDL") ? atoi(getenv("F2F_PDL")) : 3;   // programmatic dependent launch, see f2f_common.cuh
 
 namespace dn {
@@ -479,7 +480,7 @@ constexpr int NTHREADS_RAW = 11 * 32, NTHREADS_BN = 15 * 32;   // + four transfo
 constexpr int MMA_WARP = 8, TMA_A_WARP = 9, TMA_Z_WARP = 10, XF_WARP0 = 11;
 constexpr int TMEM_COLS = 128;
 // barrier slots
-constexpr int B_FULL_A = 0, B_EMPTY_A = 5, B_RAW_A = 10, B_FULL_Z = 15, B_EMPTY_Z = 18, B_TFULL = 21, B_TEMPTY = 23, B_W = 25;
+constexpr int B_FULL_A = 0, B_EMPTY_A = 5, B_RAW_A = 10, B_FULL_Z = 15, B_EMPTY_Z = 18, B_TFULL = 21, B_TEMPTY = 23, B_W = 25, B_WPEER = 26;
 static_assert(NA_MAX * A_STAGE <= 3 * A_STAGE + NZ * Z_STAGE, "the 5-stage operand ring reuses the pre-activation ring's space");
 static_assert(SMEM_BYTES <= 232448, "shared memory budget");
 static_assert(OFF_A % 1024 == 0 && OFF_Z % 1024 == 0 && A_STAGE % 1024 == 0, "swizzle alignment");
@@ -557,7 +558,7 @@ __device__ __forceinline__ void epilogue_tile(const ConvArgs &a, uint32_t tmem_a
     __syncwarp();
 }
 
-template <int PRO, int EPI>
+template <int PRO, int EPI, bool PAIR>
 __global__ void __launch_bounds__(PRO == dn::PRO_BN_RELU ? NTHREADS_BN : NTHREADS_RAW, 1)
 k_conv64t(ConvArgs a, const __grid_constant__ CUtensorMap tm_in, const __grid_constant__ CUtensorMap tm_z)
 {
@@ -570,22 +571,37 @@ k_conv64t(ConvArgs a, const __grid_constant__ CUtensorMap tm_in, const __grid_co
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + OFF_BAR);
     const uint32_t bar0 = smem_u32(bars);
     auto BAR = [&](int i) { return bar0 + 8u * i; };
-    uint32_t *tmem_ptr = reinterpret_cast<uint32_t *>(bars + 26);
+    uint32_t *tmem_ptr = reinterpret_cast<uint32_t *>(bars + 27);
+    volatile long long *tr_issue_t0 = reinterpret_cast<volatile long long *>(bars + 28);   // trace: issue start of the even tiles
     constexpr bool DGRAD = EPI == EPI_DGRAD_BN || EPI == EPI_DGRAD_RELU;
     constexpr int NA = DGRAD ? 3 : NA_MAX;
+    // PAIR: this CTA and its neighbour (cluster of 2, one TPC) run their tiles in lock-step as ONE M = 256
+    // cta_group::2 instruction stream issued by the leader (rank 0); each supplies its own operand tile and HALF of
+    // the weights (32 of the 64 output channels), so an instruction reads 4 + 1 KB of shared memory per SM instead of
+    // 4 + 2 KB.  Both run the leader's number of iterations; a tile index past the end is an all-zero tile (TMA zero
+    // fill) whose outputs are masked like any pixel outside the frame.
+    const uint32_t rank = PAIR ? cluster_ctarank() : 0u;
+    const bool leader = rank == 0;
+    const int first_tile = PAIR ? (int)(blockIdx.x & ~1u) : (int)blockIdx.x;
+    const int nit = first_tile < ntiles ? (ntiles - first_tile + (int)gridDim.x - 1) / (int)gridDim.x : 0;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < NA; s++) {
-            mbar_init(BAR(B_FULL_A + s), XF ? 128 : 1); mbar_init(BAR(B_EMPTY_A + s), 1); mbar_init(BAR(B_RAW_A + s), 1);
+            mbar_init(BAR(B_FULL_A + s), XF ? (PAIR ? 8 : 128) : 1); mbar_init(BAR(B_EMPTY_A + s), 1); mbar_init(BAR(B_RAW_A + s), 1);
         }
         for (int s = 0; s < NZ; s++) { mbar_init(BAR(B_FULL_Z + s), 1); mbar_init(BAR(B_EMPTY_Z + s), 4); }
-        for (int b = 0; b < 2; b++) { mbar_init(BAR(B_TFULL + b), 1); mbar_init(BAR(B_TEMPTY + b), 128); }
+        for (int b = 0; b < 2; b++) { mbar_init(BAR(B_TFULL + b), 1); mbar_init(BAR(B_TEMPTY + b), PAIR ? 8 : 128); }
         mbar_init(BAR(B_W), 1);
+        mbar_init(BAR(B_WPEER), 1);
         mbar_fence_init();
     }
-    if (warp == MMA_WARP) tmem_alloc(smem_u32(tmem_ptr), TMEM_COLS);
+    if (warp == MMA_WARP) {
+        if (PAIR) tmem_alloc_pair(smem_u32(tmem_ptr), TMEM_COLS);
+        else tmem_alloc(smem_u32(tmem_ptr), TMEM_COLS);
+    }
     fence_before_sync();
     __syncthreads();
+    if (PAIR) cluster_sync_all();          // the peer's barriers are initialised before anything arrives on them
     fence_after_sync();
     const uint32_t tmem_base = *tmem_ptr;
     pdl_wait();                  // everything above ran under the predecessor's tail (f2f_common.cuh)
@@ -597,16 +613,22 @@ k_conv64t(ConvArgs a, const __grid_constant__ CUtensorMap tm_in, const __grid_co
             tma_prefetch_desc(&tm_in);
             const bool tr = a.trace != nullptr;
             long long tr_wait = 0;
-            int it = 0;
-            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it++) {
+            for (int it = 0; it < nit; it++) {
+                const int tile = blockIdx.x + it * gridDim.x;
                 const int s = it % NA;
                 const int ty0 = (tile / a.tiles_x) * TH - 1, tx0 = (tile % a.tiles_x) * TW - 1;
                 const long long t0 = tr ? clock64() : 0;
                 mbar_wait(BAR(B_EMPTY_A + s), ((it / NA) & 1) ^ 1);
                 if (tr) tr_wait += clock64() - t0;
                 const uint32_t landed = BAR((XF ? B_RAW_A : B_FULL_A) + s);   // with a transform, the MMA waits for IT
-                mbar_arrive_expect_tx(landed, A_TX);
-                tma_load_3d(smem_u32(smem + OFF_A + s * A_STAGE), &tm_in, landed, 0, tx0, ty0);
+                if (PAIR && !XF) {
+                    // both CTAs' bytes are counted on the LEADER's barrier, which its MMA warp waits on
+                    if (leader) mbar_arrive_expect_tx(landed, 2 * A_TX);
+                    tma_load_3d_pair(smem_u32(smem + OFF_A + s * A_STAGE), &tm_in, mapa_u32(landed, 0), 0, tx0, ty0);
+                } else {
+                    mbar_arrive_expect_tx(landed, A_TX);
+                    tma_load_3d(smem_u32(smem + OFF_A + s * A_STAGE), &tm_in, landed, 0, tx0, ty0);
+                }
             }
             if (tr) atomicAdd(a.trace + 0, (unsigned long long)tr_wait);
         }
@@ -615,8 +637,8 @@ k_conv64t(ConvArgs a, const __grid_constant__ CUtensorMap tm_in, const __grid_co
         // ===== the layer below's pre-activation for the epilogue (16 rows x 8 pixels x 128 B) =====
         if (DGRAD && elect_one()) {
             tma_prefetch_desc(&tm_z);
-            int it = 0;
-            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it++) {
+            for (int it = 0; it < nit; it++) {
+                const int tile = blockIdx.x + it * gridDim.x;
                 const int s = it % NZ;
                 const int ty0 = (tile / a.tiles_x) * TH, tx0 = (tile % a.tiles_x) * TW;
                 mbar_wait(BAR(B_EMPTY_Z + s), ((it / NZ) & 1) ^ 1);
@@ -632,8 +654,8 @@ k_conv64t(ConvArgs a, const __grid_constant__ CUtensorMap tm_in, const __grid_co
         float sc[8], sh[8];
 #pragma unroll
         for (int j = 0; j < 8; j++) { sc[j] = a.scale[chunk * 8 + j]; sh[j] = a.shift[chunk * 8 + j]; }
-        int it = 0;
-        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it++) {
+        for (int it = 0; it < nit; it++) {
+            const int tile = blockIdx.x + it * gridDim.x;
             const int s = it % NA;
             const int ty0 = (tile / a.tiles_x) * TH - 1, tx0 = (tile % a.tiles_x) * TW - 1;
             uint8_t *st = smem + OFF_A + s * A_STAGE;
@@ -665,18 +687,37 @@ k_conv64t(ConvArgs a, const __grid_constant__ CUtensorMap tm_in, const __grid_co
                 }
             }
             fence_proxy_async();                                          // st.shared -> visible to the tensor core's reads
-            mbar_arrive(BAR(B_FULL_A + s));
+            if (PAIR) {
+                // one arrival per warp: 128 remote arrivals per tile serialise on the inter-SM path (measured)
+                __syncwarp();
+                if (lane == 0) mbar_arrive_cluster(mapa_u32(BAR(B_FULL_A + s), 0));
+            } else {
+                mbar_arrive(BAR(B_FULL_A + s));
+            }
         }
     } else if (warp == MMA_WARP) {
         // ===== MMA issuer: the warp stays converged, the elected lane issues =====
         const uint32_t el = elect_one();
         if (el) {
-            mbar_arrive_expect_tx(BAR(B_W), B_BYTES);
-            for (int t = 0; t < 9; t++) bulk_g2s(smem_u32(smem + OFF_B + t * B_TAP), a.wprep + (size_t)t * 4096, B_TAP, BAR(B_W));
+            if (PAIR) {
+                // this CTA's half of the weights: output channels 32*rank .. 32*rank+31 of every 8-channel K chunk
+                // ([tap][ic/8][oc][8] in wprep), placed at rows 0..31 of the same no-swizzle layout
+                mbar_arrive_expect_tx(BAR(B_W), B_BYTES / 2);
+                for (int c = 0; c < 72; c++)
+                    bulk_g2s(smem_u32(smem + OFF_B + c * 1024), a.wprep + (size_t)c * 512 + rank * 256, 512, BAR(B_W));
+            } else {
+                mbar_arrive_expect_tx(BAR(B_W), B_BYTES);
+                for (int t = 0; t < 9; t++) bulk_g2s(smem_u32(smem + OFF_B + t * B_TAP), a.wprep + (size_t)t * 4096, B_TAP, BAR(B_W));
+            }
         }
         __syncwarp();
         mbar_wait(BAR(B_W), 0);
-        constexpr uint32_t IDESC = idesc_h16(128, 64, 0, 0);
+        if (PAIR) {
+            if (leader) mbar_wait_cluster(BAR(B_WPEER), 0);                       // the peer's half has landed too
+            else if (el) mbar_arrive_cluster(mapa_u32(BAR(B_WPEER), 0));
+            __syncwarp();
+        }
+        constexpr uint32_t IDESC = PAIR ? idesc_h16(256, 64, 0, 0) : idesc_h16(128, 64, 0, 0);
         const uint64_t bd0 = smem_desc(smem_u32(smem + OFF_B), 1024, 128);
         const uint32_t b_lo = (uint32_t)bd0, b_hi = (uint32_t)(bd0 >> 32);
         const uint64_t ad0 = smem_desc_sw128(0, HW * 128);
@@ -689,13 +730,16 @@ k_conv64t(ConvArgs a, const __grid_constant__ CUtensorMap tm_in, const __grid_co
         unsigned long long tr_g0 = 0;
         if (tr) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tr_g0));
         int it = 0;
-        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it++) {
+        for (; it < (leader ? nit : 0); it++) {                 // the peer's MMA warp only hands over its weights
             const int s = it % NA, b = it & 1;
             const long long t0 = tr ? clock64() : 0;
-            mbar_wait(BAR(B_TEMPTY + b), ((it >> 1) & 1) ^ 1);   // accumulator drained by the epilogue
+            if (PAIR) mbar_wait_cluster(BAR(B_TEMPTY + b), ((it >> 1) & 1) ^ 1);
+            else mbar_wait(BAR(B_TEMPTY + b), ((it >> 1) & 1) ^ 1);   // accumulator drained by the epilogue
             const long long t1 = tr ? clock64() : 0;
-            mbar_wait(BAR(B_FULL_A + s), (it / NA) & 1);         // operand tile landed
+            if (PAIR) mbar_wait_cluster(BAR(B_FULL_A + s), (it / NA) & 1);
+            else mbar_wait(BAR(B_FULL_A + s), (it / NA) & 1);         // operand tile landed
             const long long t2 = tr ? clock64() : 0;
+            if (tr && b == 0) *tr_issue_t0 = t2;
             fence_after_sync();
             const uint32_t a_lo = a_lo0 | ((smem_u32(smem + OFF_A + s * A_STAGE) & 0x3FFFFu) >> 4);
             const uint32_t d0 = tmem_base + b * 64;
@@ -706,12 +750,18 @@ k_conv64t(ConvArgs a, const __grid_constant__ CUtensorMap tm_in, const __grid_co
                 for (int j = 0; j < 4; j++) {                    // K = 64 input channels = 4 x 16
                     const uint64_t bd = ((uint64_t)b_hi << 32) | (b_lo + (tap * B_TAP + j * 2 * 1024) / 16);
                     const uint64_t ad = ((uint64_t)a_hi << 32) | (a_lo + (dy * HW + dx) * 8 + j * 2);
-                    mma_ss_el(d0, ad, bd, IDESC, (tap | j) != 0, el);
+                    if (PAIR) mma_ss_el_pair(d0, ad, bd, IDESC, (tap | j) != 0, el);
+                    else mma_ss_el(d0, ad, bd, IDESC, (tap | j) != 0, el);
                 }
             }
             if (el) {
-                mma_commit(BAR(B_EMPTY_A + s));
-                mma_commit(BAR(B_TFULL + b));
+                if (PAIR) {
+                    mma_commit_pair(BAR(B_EMPTY_A + s));
+                    mma_commit_pair(BAR(B_TFULL + b));
+                } else {
+                    mma_commit(BAR(B_EMPTY_A + s));
+                    mma_commit(BAR(B_TFULL + b));
+                }
             }
             __syncwarp();
             if (tr) { tr_te += t1 - t0; tr_full += t2 - t1; tr_issue += clock64() - t2; }
@@ -744,19 +794,28 @@ k_conv64t(ConvArgs a, const __grid_constant__ CUtensorMap tm_in, const __grid_co
         const bool tr = a.trace != nullptr && threadIdx.x == 0;
         long long tr_wait = 0, tr_work = 0;
         const long long tr_start = tr ? clock64() : 0;
-        int it = set, ntr = 0;
-        for (int tile = blockIdx.x + set * gridDim.x; tile < ntiles; tile += 2 * gridDim.x, it += 2) {
+        int ntr = 0;
+        for (int it = set; it < nit; it += 2) {
+            const int tile = blockIdx.x + it * gridDim.x;
             const int sz = it % NZ;
             const int ty = (tile / a.tiles_x) * TH, tx = (tile % a.tiles_x) * TW;
             const long long t0 = tr ? clock64() : 0;
             mbar_wait(BAR(B_TFULL + set), (it >> 1) & 1);
             const long long t1 = tr ? clock64() : 0;
+            if (tr && leader) {      // first MMA of the tile issued -> its completion seen here (same SM, same clock)
+                atomicAdd(a.trace + 12, (unsigned long long)(t1 - *tr_issue_t0)); atomicAdd(a.trace + 13, 1ull);
+            }
             fence_after_sync();
             epilogue_tile<EPI>(a, tmem_base + ((uint32_t)(wq * 32) << 16) + set * 64, stg, smem + OFF_Z + sz * Z_STAGE,
                                BAR(B_FULL_Z + sz), (it / NZ) & 1, lane, wq, ty, tx, acc0, acc1, cf);
             if (DGRAD && lane == 0) mbar_arrive(BAR(B_EMPTY_Z + sz));
             fence_before_sync();
-            mbar_arrive(BAR(B_TEMPTY + set));
+            if (PAIR) {
+                __syncwarp();
+                if (lane == 0) mbar_arrive_cluster(mapa_u32(BAR(B_TEMPTY + set), 0));
+            } else {
+                mbar_arrive(BAR(B_TEMPTY + set));
+            }
             if (tr) { tr_wait += t1 - t0; tr_work += clock64() - t1; ntr++; }
         }
         if (tr) {
@@ -791,7 +850,11 @@ k_conv64t(ConvArgs a, const __grid_constant__ CUtensorMap tm_in, const __grid_co
     }
     fence_before_sync();
     __syncthreads();
-    if (warp == MMA_WARP) tmem_dealloc(tmem_base, TMEM_COLS);
+    if (PAIR) cluster_sync_all();          // neither CTA leaves while the other may still arrive on its barriers
+    if (warp == MMA_WARP) {
+        if (PAIR) tmem_dealloc_pair(tmem_base, TMEM_COLS);
+        else tmem_dealloc(tmem_base, TMEM_COLS);
+    }
 }
 
 // NHWC BF16 image [H][W][64] as a 3-D tensor (channels, x, y), 128-byte swizzle, box = boxw x boxh pixels
@@ -831,7 +894,8 @@ static int launch_conv64t(ConvArgs a, cudaStream_t st)
 {
     static bool configured = false;
     if (!configured) {
-        F2F_CUDA_CHECK(cudaFuncSetAttribute(k_conv64t<PRO, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        F2F_CUDA_CHECK(cudaFuncSetAttribute(k_conv64t<PRO, EPI, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        F2F_CUDA_CHECK(cudaFuncSetAttribute(k_conv64t<PRO, EPI, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
         configured = true;
     }
     a.tiles_x = cdiv(a.W, TW);
@@ -847,10 +911,13 @@ static int launch_conv64t(ConvArgs a, cudaStream_t st)
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const int ntiles = a.tiles_x * a.tiles_y;
     const int grid = ntiles < sms ? ntiles : sms;
+    const dim3 block(PRO == dn::PRO_BN_RELU ? NTHREADS_BN : NTHREADS_RAW);
     prof_begin(0, st);
     a.pdl_trigger = (g_pdl >> 2) & 1;
-    F2F_CUDA_CHECK(launch_pdl(1, k_conv64t<PRO, EPI>, dim3(grid), dim3(PRO == dn::PRO_BN_RELU ? NTHREADS_BN : NTHREADS_RAW),
-                              SMEM_BYTES, st, a, tm_in, tm_z));
+    if (g_conv_pair)      // an even number of CTAs: the last pair's second CTA may only have all-zero tiles
+        F2F_CUDA_CHECK(launch_pdl_pairs(1, k_conv64t<PRO, EPI, true>, dim3((grid + 1) & ~1), block, SMEM_BYTES, st, a, tm_in, tm_z));
+    else
+        F2F_CUDA_CHECK(launch_pdl(1, k_conv64t<PRO, EPI, false>, dim3(grid), block, SMEM_BYTES, st, a, tm_in, tm_z));
     prof_end(0, st);
     g_dncnn_launches++;
     F2F_LAUNCH_CHECK();
@@ -928,6 +995,7 @@ void f2f_profile_dncnn_read(double out[4])
 
 void f2f_dncnn_set_trace(unsigned long long *d_counters) { g_conv_trace = d_counters; }
 void f2f_set_pdl(int on) { f2f::g_pdl = on; }
+void f2f_set_conv_pair(int on) { f2f::g_conv_pair = on; }
 int f2f_dncnn_storage_dtype(void) { return tc05::H16_FORMAT ? 0 : 1; }
 void f2f_dncnn_set_legacy(int on) { g_conv_legacy = on != 0; }
 

@@ -36,6 +36,7 @@ void prof_end(int cls, cudaStream_t st);
 // bit 3 in the small ones.  Measured at 1080p on one box (train iteration, profiles/r01_pdl_ab.log): 0 (fully
 // serialised) 9.03 ms, 3 (default: attributes only) 8.69 ms, 11 8.69 ms, 15 (all early triggers) 9.28 ms -- releasing
 // the dependents early from a persistent kernel that owns every SM only parks their CTAs, so it is off.
+extern int g_conv_pair;   // 1: the 64->64 convolutions run as CTA pairs (cta_group::2), F2F_CONV_PAIR / f2f_set_conv_pair
 extern int g_pdl;   // bit 0: attribute on the big kernels, 1: on the small ones, 2: early trigger in the big, 3: in the small
 template <class... KArgs, class... Args>
 static inline cudaError_t launch_pdl(int big, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args)
@@ -46,6 +47,22 @@ static inline cudaError_t launch_pdl(int big, void (*kernel)(KArgs...), dim3 gri
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = (g_pdl >> (big ? 0 : 1)) & 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
+// The same launch as a grid of CTA pairs (clusters of 2 along x: the two SMs of a TPC), for cta_group::2 kernels.
+template <class... KArgs, class... Args>
+static inline cudaError_t launch_pdl_pairs(int big, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                           Args... args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = (g_pdl >> (big ? 0 : 1)) & 1;
+    attr[1].id = cudaLaunchAttributeClusterDimension;
+    attr[1].val.clusterDim.x = 2; attr[1].val.clusterDim.y = 1; attr[1].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 2;
     return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
 }
 

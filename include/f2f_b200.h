@@ -224,6 +224,10 @@ void f2f_dncnn_set_legacy(int on);
  * and the small kernels, no early trigger); 0 launches the same kernels fully serialised (F2F_PDL in the environment
  * sets the initial value).  Results are identical, only the gaps between kernels differ (csrc/f2f_common.cuh). */
 void f2f_set_pdl(int on);
+/* Experimental: on != 0 runs the 64->64 convolutions (forward and input gradient) as CTA pairs -- clusters of two
+ * CTAs issuing one tcgen05.mma.cta_group::2 M = 256 instruction stream, each CTA supplying half of the weights
+ * (F2F_CONV_PAIR in the environment sets the initial value, default 0).  Same results bit for bit. */
+void f2f_set_conv_pair(int on);
 /* 16-bit storage type the library was built with for DnCNN activations, gradients and tensor-core operands:
  * 1 = FP16 (default), 0 = BF16 (-DF2F_STORE_BF16, frame2frame_b200/build.py F2F_STORE_BF16=1).  Callers that
  * pre-pack operand buffers (f2f_dncnn_conv64 / dgrad64 / wgrad64) must use this type. */

@@ -56,6 +56,7 @@ for name, fn in [("conv raw/store", conv(0, 0)), ("conv raw/stats", conv(0, 1)),
     else:
         ptiles = (tiles + 1) // 2     # the traced producer thread stages every other tile
         per = [t[0] / ptiles, t[1] / ptiles] + [v / tiles for v in t[2:8]]
+    exec_cyc = t[12] / max(t[13], 1)          # issue of a tile's first MMA -> its completion seen by the epilogue
     mhz_single = t[10] / max(t[11], 1) * 1e3
     # the same with the trace armed over 20 back-to-back launches: the SM clock the kernel sustains (power cap)
     tr.zero_()
@@ -70,5 +71,6 @@ for name, fn in [("conv raw/store", conv(0, 0)), ("conv raw/stats", conv(0, 1)),
     mhz_sust = t2[10] / max(t2[11], 1) * 1e3
     print("%-15s %7.1f us %6.0f TFLOP/s | cycles/tile: " % (name, us, 2 * 9 * 64 * 64 * H * W / us / 1e6) +
           "  ".join("%s %.0f" % (n, v) for n, v in zip(names, per)) + "  (%d tiles)" % tiles +
+          " | first MMA issued -> tile complete %.0f cycles" % exec_cyc +
           " | SM clock: isolated launch %.0f MHz, 20 back-to-back %.0f MHz (%.1f us/launch, %.0f cycles/tile)"
           % (mhz_single, mhz_sust, us20, (t2[2] + t2[3] + t2[4]) / max(t2[8], 1)))
