@@ -1,4 +1,5 @@
 #!/bin/bash
+# (historical: recorded when BF16 was the default and F2F_STORE_FP16=1 selected FP16; FP16 is now the default and F2F_STORE_BF16=1 selects BF16)
 # GPU call: FP16 instead of BF16 storage of the DnCNN tensors (same tensor-core rate) -- kernel parity, speed, and the
 # PSNR parity of the online loop at 540x960 against the FP32 CPU oracle, next to the BF16 build on the same box
 mkdir -p gpurun_out
