@@ -258,8 +258,25 @@ def ours_batch(args, rank, world, local_rank, ClockSampler, peaks):
         eng.finetune(currs, prevs, [flow] * len(currs), ITERS)
         return [eng.denoise(c) for c in currs]
 
+    # end-to-end leg: the same step from pinned host frames (H2D of curr and prev of every local sequence) to
+    # pinned host results (D2H of every denoised frame) inside the timed region
+    host = {s: [f.cpu().pin_memory() for f in frames[s]] for s in eng.local}
+    out_host = [torch.empty((1, 1, H, W), dtype=torch.float32).pin_memory() for _ in eng.local]
+
+    def step_host(k):
+        currs = [host[s][(k + 1) % nf].to(dev, non_blocking=True) for s in eng.local]
+        prevs = [host[s][k % nf].to(dev, non_blocking=True) for s in eng.local]
+        eng.finetune(currs, prevs, [flow] * len(currs), ITERS)
+        for o, c in zip(out_host, currs):
+            o.copy_(eng.denoise(c), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
     for k in range(args.warmup):
         step(k)
+    lib = _lib.lib()
+    prof = (C.c_double * 5)()
+    lib.f2f_profile_read(prof)
+    launches_before = prof[4]
     barrier()
     sampler = ClockSampler(local_rank) if rank == 0 else None
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -274,6 +291,18 @@ def ours_batch(args, rank, world, local_rank, ClockSampler, peaks):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_max = float(t.item())
+    lib.f2f_profile_read(prof)
+    launches = prof[4] - launches_before
+    step_host(args.warmup + args.steps)
+    barrier()
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        step_host(args.warmup + k)
+    dt = time.perf_counter() - t0
+    t = torch.tensor([dt], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = NSEQ * args.steps / float(t.item())
     if rank != 0:
         return
     value = NSEQ * args.steps / (ms_max * 1e-3)
@@ -292,6 +321,10 @@ def ours_batch(args, rank, world, local_rank, ClockSampler, peaks):
                    "frame": "%dx%d" % (W, H), "iter": ITERS, "sequences": NSEQ,
                    "l2": "inputs larger than L2 (265 MB per activation)"},
         "clocks": clocks, "model_tflops_per_gpu": tf,
+        "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": 2 * NSEQ * H * W * 4,
+                "d2h_bytes_per_step": NSEQ * H * W * 4,
+                "api": "BatchF2F.finetune + denoise (frame2frame_b200/batch_f2f.py) from/to pinned host frames"},
+        "gpu_launches": int(launches),
         "roofline": {"bound": "tensor", "kernel": "whole train step (model FLOPs)", "achieved": tf, "peak": peak_tf,
                      "peak_source": pk_kind + " bf16_tflops_sustained", "unit": "TFLOP/s", "frac": tf / peak_tf, "traffic": None},
     }
