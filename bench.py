@@ -40,6 +40,26 @@ ALG_BYTES_PER_PX_ITER = 64   # read rho_c,I1wx,I1wy,grad,u1,u2,p11..p
 from frame2frame_b200.benchutil import ClockSampler, peaks  # noqa: E402
 
 
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """File descriptor 1 -> stderr for the duration of the run; emit() writes the JSON line to the real stdout."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(obj):
+    sys.stdout.flush()
+    if _REAL_STDOUT is not None:
+        os.dup2(_REAL_STDOUT, 1)
+    print(json.dumps(obj), flush=True)
+    if _REAL_STDOUT is not None:
+        os.dup2(2, 1)
+
+
 def make_pairs(n, seq):
     """n consecutive synthetic 1080p frame pairs (I0 = frame t+1, I1 = frame t: the
     backward flow tvl1flow.sh:11-14 computes)."""
@@ -76,7 +96,7 @@ def reference_arm(args, rank, world):
         run(I0[(args.warmup + k) % len(I0)], I1[(args.warmup + k) % len(I0)])
     dt = time.perf_counter() - t0
     v = args.steps / dt
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": "TV-L1 flow fields/sec @1080p gray", "value": v, "unit": "fields/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -85,7 +105,7 @@ def reference_arm(args, rank, world):
         "cpu_baseline": {"value": v, "unit": "fields/s", "cores": cores, "kind": kind,
                          "sample": "%d x 1 pair 1920x1080, OpenMP %d threads" % (args.steps, cores)},
         "e2e": {"value": v, "unit": "fields/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }))
+    })
 
 
 def cpu_baseline(seconds_budget=25.0):
@@ -232,6 +252,10 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     import bench_f2f
+    # stdout carries the JSON line and nothing else: libraries that write to file descriptor 1 on their own (NCCL's
+    # version banner under torchrun) are sent to stderr for the duration of the run
+    quiet_stdout()
+    bench_f2f.emit = emit
     if args.impl == "reference":
         if args.workload == "f2f":
             bench_f2f.reference_arm(args, rank, world)
@@ -261,7 +285,7 @@ def main():
                     line["tvl1"] = {k: t[k] for k in ("metric", "value", "unit", "ms_per_step", "config", "e2e", "roofline",
                                                       "cpu_baseline") if k in t}
         if rank == 0:
-            print(json.dumps(line))
+            emit(line)
     finally:
         if world > 1:
             import torch.distributed as dist
