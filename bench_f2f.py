@@ -64,14 +64,35 @@ def _oracle_frame_seconds(torch, cores, train_iters=1):
     return (t1 - t0) / train_iters, t2 - t1
 
 
+def _oracle_flow_seconds(cores):
+    """The frame's backward TV-L1 flow on the host cores: the reference's own tvl1flow_lib.c (oracle/_ref, OpenMP) when
+    it is built, else the C restatement -- one 1080p pair with the parameters the device path uses (FLOW_KW)."""
+    from frame2frame_b200 import synth
+    from oracle.tvl1 import OracleTvl1, RefTvl1
+    os.environ["OMP_NUM_THREADS"] = str(cores)          # torchrun exports OMP_NUM_THREADS=1
+    f = [synth.noisy_frame(H, W, t) for t in range(2)]
+    if RefTvl1.available():
+        RefTvl1.set_threads(cores)
+        impl = RefTvl1()
+        t0 = time.perf_counter()
+        impl.flow(f[1], f[0], **FLOW_KW)
+    else:
+        impl = OracleTvl1()
+        t0 = time.perf_counter()
+        impl.flow(f[1], f[0], **FLOW_KW)
+    return time.perf_counter() - t0
+
+
 def cpu_baseline():
     import torch
     cores = os.cpu_count() or 1
     t_it, t_ev = _oracle_frame_seconds(torch, cores, 1)
-    sec = ITERS * t_it + t_ev
+    t_fl = _oracle_flow_seconds(cores)
+    sec = ITERS * t_it + t_ev + t_fl
     return {"value": 1.0 / sec, "unit": "frames/s", "cores": cores, "kind": "port",
-            "sample": "1 fine-tuning iteration (%.1f s) + 1 eval forward (%.1f s) of one 1920x1080 frame, torch %s CPU FP32 "
-                      "%d threads; extrapolated to iter=20 per frame" % (t_it, t_ev, torch.__version__, cores)}
+            "sample": "1 fine-tuning iteration (%.1f s) + 1 eval forward (%.1f s) + the TV-L1 flow (%.1f s, tvl1flow_lib.c) of "
+                      "one 1920x1080 frame, torch %s CPU FP32 %d threads; extrapolated to iter=20 per frame"
+                      % (t_it, t_ev, t_fl, torch.__version__, cores)}
 
 
 def reference_arm(args, rank, world):
@@ -81,21 +102,22 @@ def reference_arm(args, rank, world):
     cores = os.cpu_count() or 1
     for _ in range(min(args.warmup, 1)):
         _oracle_frame_seconds(torch, cores, 1)
-    t_it = t_ev = 0.0
+    t_it = t_ev = t_fl = 0.0
     for _ in range(args.steps):
         a, b = _oracle_frame_seconds(torch, cores, 1)
         t_it += a
         t_ev += b
-    sec = (ITERS * t_it + t_ev) / args.steps
+        t_fl += _oracle_flow_seconds(cores)
+    sec = (ITERS * t_it + t_ev + t_fl) / args.steps
     v = 1.0 / sec
     emit({
         "impl": "reference", "metric": METRIC, "value": v, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": "configs[2]: online F2F denoise, 1080p gray sigma=25 synthetic seq, DnCNN-25, iter=20 per frame "
-                               "(bounded sample per step: 1 fine-tuning iteration + 1 eval forward, extrapolated to iter=20)"},
+                               "(bounded sample per step: 1 fine-tuning iteration + 1 eval forward + the frame's TV-L1 flow, extrapolated to iter=20)"},
         "cpu_baseline": {"value": v, "unit": "frames/s", "cores": cores, "kind": "port",
-                         "sample": "%d x (1 iteration + 1 eval forward) of a 1920x1080 frame, torch CPU FP32 %d threads; the "
+                         "sample": "%d x (1 iteration + 1 eval forward + TV-L1 flow) of a 1920x1080 frame, torch CPU FP32 %d threads; the "
                                    "reference's DnCNN submodule is un-vendored, so its loop is restated with the same stock "
                                    "torch modules (oracle/dncnn_oracle.py)" % (args.steps, cores)},
         "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
