@@ -226,12 +226,13 @@ def ours_tvl1(args, rank, world, local_rank, with_cpu=True):
         "roofline": {"bound": "hbm", "kernel": "k_iter_strip<4> (fused primal-dual iteration, finest scale)",
                      "achieved": achieved, "peak": pk["hbm_gbs"], "peak_source": pk_kind, "unit": "GB/s",
                      "frac": (achieved / pk["hbm_gbs"]) if achieved else None,
+                     "frac_of_nominal_8TBs": (achieved / 8000.0) if achieved else None,
                      "alg_bytes_per_px_iter": ALG_BYTES_PER_PX_ITER,
                      "px_iters_per_step": px0 * slot_iters0 / args.steps,
                      "launches_per_step": launches0 / args.steps,
                      "avg_launch_us": iter_ms * 1e3 / launches0 if launches0 else None,
                      "traffic": 2.148e9, "traffic_note": "dram read+write per launch of 16 slots, ncu --set full, "
-                                                         "profiles/r01_tvl1_iter_strip.md"},
+                                                         "profiles/r01_ncu_tvl1_iter_strip.txt"},
     }
     if world == 1 and not args.no_cpu and with_cpu:
         line["cpu_baseline"] = cpu_baseline()

@@ -7,6 +7,8 @@ import numpy as np, torch
 from frame2frame_b200 import synth
 from oracle import dncnn_oracle as do, dncnn_bf16 as db, f2f_oracle as fo
 
+if os.environ.get("F2F_EMU_STORAGE", "bf16") == "fp16":      # emulate the FP16 (default) build instead of the BF16 one
+    db.STORAGE = torch.float16
 H, W, NF, ITERS = (int(v) for v in sys.argv[1:5])
 variants = sys.argv[5:] or ["w+act+grad", "w", "act", "grad", "none"]
 sd = synth.pretrained_state_dict()
