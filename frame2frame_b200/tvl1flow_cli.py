@@ -45,16 +45,24 @@ def parse_positionals(argv):
     return vals
 
 
-def main(argv=None):
+def plan_sequence(first, last, out):
+    """tvl1flow.sh:9-19 as a list of (index of I0, index of I1, output file): for every i in first..last the backward
+    flow (I0 = frame i+1, I1 = frame i) to out % (i+1) + "_bflow.flo", then the forward flow to out % i + "_fflow.flo"."""
+    jobs = []
+    for i in range(first, last + 1):
+        jobs.append((i + 1, i, (out % (i + 1)) + "_bflow.flo"))
+        jobs.append((i, i + 1, (out % i) + "_fflow.flo"))
+    return jobs
+
+
+def main(argv=None, device=None):
     argv = list(sys.argv[1:] if argv is None else argv)
-    dev = torch.device("cuda", 0)
+    dev = torch.device("cuda", 0) if device is None else torch.device(device)
     if argv and argv[0] == "--sequence":
         pattern, first, last, out = argv[1], int(argv[2]), int(argv[3]), argv[4]
         frames = {i: read_gray(pattern % i) for i in range(first, last + 2)}
-        I0, I1, names = [], [], []
-        for i in range(first, last + 1):
-            I0.append(frames[i + 1]); I1.append(frames[i]); names.append((out % (i + 1)) + "_bflow.flo")
-            I0.append(frames[i]); I1.append(frames[i + 1]); names.append((out % i) + "_fflow.flo")
+        jobs = plan_sequence(first, last, out)
+        I0, I1, names = [frames[a] for a, _, _ in jobs], [frames[b] for _, b, _ in jobs], [n for _, _, n in jobs]
         flow = tvl1flow(torch.from_numpy(np.stack(I0)).to(dev), torch.from_numpy(np.stack(I1)).to(dev), **SCRIPT_PARAMS)
         for f, name in zip(flow, names):
             write_flo(name, f)

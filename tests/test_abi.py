@@ -85,3 +85,30 @@ def test_tvl1flow_cli_positionals_follow_main_c():
             v["epsilon"], v["verbose"]) == ("out.flo", 8, 0.2, 0.1, 0.4, 5, 1, 0.6, 3, 0.02, 1)
     with pytest.raises(SystemExit):
         tvl1flow_cli.parse_positionals(["only_one.png"])
+
+
+def test_tvl1flow_cli_sequence_follows_the_script(tmp_path, monkeypatch):
+    """tvl1flow.sh:9-19 -- pair order, file names and parameters of the sequence mode; the solver is replaced by a
+    recorder, so this runs without a GPU."""
+    import numpy as np
+    import torch
+    from frame2frame_b200 import tvl1flow_cli as cli
+    assert cli.plan_sequence(3, 4, "o/%03d") == [(4, 3, "o/004_bflow.flo"), (3, 4, "o/003_fflow.flo"),
+                                                 (5, 4, "o/005_bflow.flo"), (4, 5, "o/004_fflow.flo")]
+    for i in range(1, 4):
+        np.save(tmp_path / ("f%03d.npy" % i), np.full((6, 8), float(i), np.float32))
+    calls, written = [], {}
+
+    def fake_flow(I0, I1, **kw):
+        calls.append((I0[:, 0, 0].tolist(), I1[:, 0, 0].tolist(), kw))
+        return torch.stack([torch.full((2, 6, 8), float(k)) for k in range(I0.shape[0])])
+
+    monkeypatch.setattr(cli, "tvl1flow", fake_flow)
+    monkeypatch.setattr(cli, "write_flo", lambda name, f: written.__setitem__(name, float(f[0, 0, 0])))
+    out = str(tmp_path / "o%03d")
+    assert cli.main(["--sequence", str(tmp_path / "f%03d.npy"), "1", "2", out], device="cpu") == 0
+    (i0, i1, kw), = calls
+    assert i0 == [2.0, 1.0, 3.0, 2.0] and i1 == [1.0, 2.0, 2.0, 3.0]         # bflow(1), fflow(1), bflow(2), fflow(2)
+    assert kw == dict(tau=0.25, lam=0.2, theta=0.3, nscales=100, fscale=2, zfactor=0.5, nwarps=5, epsilon=0.01)
+    assert written == {out % 2 + "_bflow.flo": 0.0, out % 1 + "_fflow.flo": 1.0, out % 3 + "_bflow.flo": 2.0,
+                       out % 2 + "_fflow.flo": 3.0}
