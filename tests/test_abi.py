@@ -1,5 +1,6 @@
 """CPU tests of the drop-in boundary: the C-ABI library loads and exports every
 symbol include/f2f_b200.h declares; host-side parameter logic (no compute)."""
+import os
 import ctypes as C
 
 import numpy as np
@@ -112,3 +113,24 @@ def test_tvl1flow_cli_sequence_follows_the_script(tmp_path, monkeypatch):
     assert kw == dict(tau=0.25, lam=0.2, theta=0.3, nscales=100, fscale=2, zfactor=0.5, nwarps=5, epsilon=0.01)
     assert written == {out % 2 + "_bflow.flo": 0.0, out % 1 + "_fflow.flo": 1.0, out % 3 + "_bflow.flo": 2.0,
                        out % 2 + "_fflow.flo": 3.0}
+
+
+def test_missing_library_fails_loudly_no_cpu_fallback():
+    """The product path has no CPU fallback: without libf2f_b200.so the first call raises."""
+    import subprocess
+    import sys
+    code = ("from frame2frame_b200 import _lib\n"
+            "try:\n    _lib.lib()\nexcept RuntimeError as e:\n    print('RAISED', e)\n")
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=120,
+                       env=dict(os.environ, F2F_LIB="/nonexistent/libf2f_b200.so"),
+                       cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    assert "RAISED" in r.stdout and "no CPU fallback" in r.stdout, r.stdout + r.stderr
+
+
+def test_cuda_ops_refuse_cpu_tensors():
+    """warp / DnCNN on CPU tensors raise instead of computing on the host."""
+    import pytest
+    import torch
+    from frame2frame_b200.warped_loss import warp_mask
+    with pytest.raises((RuntimeError, ValueError)):
+        warp_mask(torch.zeros(1, 1, 8, 8), torch.zeros(1, 2, 8, 8))
