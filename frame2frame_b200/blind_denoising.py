@@ -233,6 +233,51 @@ def blind_denoising(**args):
     plot_psnr.close()
 
 
+# ------------------------------------------------------------------ frame chunks over GPUs
+def chunk_bounds(first, last, rank, world):
+    """The online loop does not shard inside a stream (weights, Adam and BatchNorm state carry from frame to frame),
+    so several GPUs take independent --first/--last chunks, each restarting from the pretrained weights -- the
+    reference's own way of splitting a sequence (blind_denoising.py:279-282; SURVEY 8e, configs[4]).  Frames
+    first+1 .. last are the denoised ones (blind_denoising.py:187); rank `rank` of `world` takes a contiguous block
+    of them and starts ONE frame earlier: that frame is only its first `prev`.  -> (first_r, last_r), or None when
+    there are fewer frames than ranks and this rank has none."""
+    n = max(last - first, 0)
+    base, extra = divmod(n, world)
+    count = base + (1 if rank < extra else 0)
+    if count == 0:
+        return None
+    lo = first + 1 + rank * base + min(rank, extra)
+    return lo - 1, lo + count - 1
+
+
+def _chunk_name(path, rank):
+    root, ext = os.path.splitext(path)
+    return "%s.chunk%03d%s" % (root, rank, ext)
+
+
+def run_chunked(args, rank, world, run=None, barrier=None, local_rank=None):
+    """One rank's share of blind_denoising(**args) under `world` processes (torchrun): its chunk of frames on its own
+    GPU, output frames under the usual names, its network under `output_network` + '.chunkRRR', and its PSNR lines in
+    a part file that rank 0 concatenates in frame order into `output_psnr` once every rank is done."""
+    run = blind_denoising if run is None else run
+    part = _chunk_name(args["output_psnr"], rank)
+    b = chunk_bounds(args["first"], args["last"], rank, world)
+    if b is None:
+        open(part, "w").close()
+    else:
+        run(**dict(args, first=b[0], last=b[1], output_psnr=part, output_network=_chunk_name(args["output_network"], rank),
+                   gpu=rank if local_rank is None else local_rank))
+    if barrier is not None:
+        barrier()
+    if rank == 0:
+        with open(args["output_psnr"], "w") as out:
+            for r in range(world):
+                fn = _chunk_name(args["output_psnr"], r)
+                with open(fn) as f:
+                    out.write(f.read())
+                os.remove(fn)
+
+
 def main(argv=None):
     parser = argparse.ArgumentParser(description="Blind_denoising")
     parser.add_argument("--input", type=str, default="", help="path to input frames (C type)")
@@ -254,6 +299,18 @@ def main(argv=None):
     for p, v in zip(argspar.__dict__.keys(), argspar.__dict__.values()):
         print("\t{}: {}".format(p, v))
     print("\n")
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world > 1:
+        # launched with torchrun: one process per GPU, every rank an independent chunk of the sequence; the only
+        # exchange is the barrier before rank 0 assembles the PSNR file (gloo: nothing on the data path)
+        import torch.distributed as dist
+        dist.init_process_group("gloo")
+        try:
+            run_chunked(vars(argspar), int(os.environ["RANK"]), world, barrier=dist.barrier,
+                        local_rank=int(os.environ.get("LOCAL_RANK", "0")))
+        finally:
+            dist.destroy_process_group()
+        return
     blind_denoising(**vars(argspar))
 
 
