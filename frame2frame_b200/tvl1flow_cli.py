@@ -8,8 +8,9 @@ device has no OpenMP thread count); reads two images, writes a Middlebury ``.flo
 backward flow (I0 = frame i+1, I1 = frame i) to ``O % (i+1) + "_bflow.flo"`` and the forward flow to
 ``O % i + "_fflow.flo"``, with the script's parameters (lambda 0.2, nscales 100 -> clamp, fscale 2).  All 2*(L-F+1)
 pairs go through ONE batched call (frame pairs are independent; slots advance in lock-step on the device) instead
-of one process per pair.
+of one process per pair.  Started under torchrun, every rank takes a contiguous block of the pairs on its own GPU.
 """
+import os
 import sys
 
 import numpy as np
@@ -55,13 +56,24 @@ def plan_sequence(first, last, out):
     return jobs
 
 
+def shard_jobs(jobs, rank, world):
+    """Frame pairs are independent: rank `rank` of `world` takes a contiguous block of the job list."""
+    base, extra = divmod(len(jobs), world)
+    lo = rank * base + min(rank, extra)
+    return jobs[lo:lo + base + (1 if rank < extra else 0)]
+
+
 def main(argv=None, device=None):
     argv = list(sys.argv[1:] if argv is None else argv)
-    dev = torch.device("cuda", 0) if device is None else torch.device(device)
+    # under torchrun every rank computes its own block of pairs on GPU LOCAL_RANK; nothing is exchanged
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0"))) if device is None else torch.device(device)
     if argv and argv[0] == "--sequence":
         pattern, first, last, out = argv[1], int(argv[2]), int(argv[3]), argv[4]
-        frames = {i: read_gray(pattern % i) for i in range(first, last + 2)}
-        jobs = plan_sequence(first, last, out)
+        jobs = shard_jobs(plan_sequence(first, last, out), rank, world)
+        if not jobs:
+            return 0
+        frames = {i: read_gray(pattern % i) for i in sorted({a for a, _, _ in jobs} | {b for _, b, _ in jobs})}
         I0, I1, names = [frames[a] for a, _, _ in jobs], [frames[b] for _, b, _ in jobs], [n for _, _, n in jobs]
         flow = tvl1flow(torch.from_numpy(np.stack(I0)).to(dev), torch.from_numpy(np.stack(I1)).to(dev), **SCRIPT_PARAMS)
         for f, name in zip(flow, names):

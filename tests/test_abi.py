@@ -134,3 +134,24 @@ def test_cuda_ops_refuse_cpu_tensors():
     from frame2frame_b200.warped_loss import warp_mask
     with pytest.raises((RuntimeError, ValueError)):
         warp_mask(torch.zeros(1, 1, 8, 8), torch.zeros(1, 2, 8, 8))
+
+
+def test_tvl1flow_cli_sequence_shards_pairs_over_ranks(tmp_path, monkeypatch):
+    """Under torchrun (RANK / WORLD_SIZE) the sequence mode splits the pair list into contiguous blocks, one per rank;
+    together the ranks write every file of the single-process run exactly once."""
+    import numpy as np
+    import torch
+    from frame2frame_b200 import tvl1flow_cli as cli
+    jobs = cli.plan_sequence(1, 5, "o%03d")
+    assert sum((cli.shard_jobs(jobs, r, 4) for r in range(4)), []) == jobs
+    assert [len(cli.shard_jobs(jobs, r, 4)) for r in range(4)] == [3, 3, 2, 2]
+    assert cli.shard_jobs(jobs[:1], 1, 2) == []
+    for i in range(1, 5):
+        np.save(tmp_path / ("f%03d.npy" % i), np.full((4, 4), float(i), np.float32))
+    written = []
+    monkeypatch.setattr(cli, "tvl1flow", lambda I0, I1, **kw: torch.zeros(I0.shape[0], 2, 4, 4))
+    monkeypatch.setattr(cli, "write_flo", lambda name, f: written.append(os.path.basename(name)))
+    for rank in range(3):
+        monkeypatch.setenv("RANK", str(rank)); monkeypatch.setenv("WORLD_SIZE", "3")
+        assert cli.main(["--sequence", str(tmp_path / "f%03d.npy"), "1", "3", str(tmp_path / "o%03d")], device="cpu") == 0
+    assert written == ["o002_bflow.flo", "o001_fflow.flo", "o003_bflow.flo", "o002_fflow.flo", "o004_bflow.flo", "o003_fflow.flo"]
