@@ -31,3 +31,39 @@ def test_reference_arm_other_ranks_stay_silent():
     r = _run({"RANK": "1", "LOCAL_RANK": "1", "WORLD_SIZE": "2"}, "--gpus", "2")
     assert r.returncode == 0, r.stderr[-2000:]
     assert r.stdout.strip() == ""
+
+
+def test_clock_sampler_parses_nvidia_smi_lines():
+    from frame2frame_b200.benchutil import ClockSampler
+
+    class FakeProc:
+        def terminate(self):
+            pass
+
+    s = ClockSampler.__new__(ClockSampler)
+    s.proc = FakeProc()
+    s.samples = ["1965, 1965, Not Active, Not Active, Not Active, Not Active",
+                 "1530, 1965, Not Active, Not Active, Not Active, Active",
+                 "1500, 1965, Not Active, Not Active, Not Active, Active",
+                 "garbage", "[N/A], 1965, Not Active, Not Active, Not Active, Not Active"]
+    c = s.stop()
+    assert c == {"sm_mhz": 1530.0, "sm_max_mhz": 1965.0, "reasons": ["sw_power_cap"], "samples": 3}
+
+
+def test_clock_sampler_without_nvidia_smi_says_so():
+    import shutil
+    import pytest
+    from frame2frame_b200.benchutil import ClockSampler
+    if shutil.which("nvidia-smi"):
+        pytest.skip("nvidia-smi present")
+    assert ClockSampler(0).stop()["reasons"] == ["nvidia-smi unavailable"]
+
+
+def test_peaks_fall_back_when_the_driver_file_is_absent(tmp_path, monkeypatch):
+    from frame2frame_b200 import benchutil
+    monkeypatch.setattr(benchutil, "ROOT", str(tmp_path))
+    pk, kind = benchutil.peaks()
+    assert kind == "fallback" and pk["hbm_gbs"] > 0 and pk["bf16_tflops_sustained"] <= pk["bf16_tflops"]
+    (tmp_path / "MEASURED_PEAKS.json").write_text('{"hbm_gbs": 6551.7, "bf16_tflops": 1630.0, "bf16_tflops_sustained": 1385.1}')
+    pk, kind = benchutil.peaks()
+    assert kind == "measured" and pk["hbm_gbs"] == 6551.7
