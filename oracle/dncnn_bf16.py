@@ -26,7 +26,9 @@ def bf(t):
 # Which classes of tensors are rounded to BF16 (all of them = the CUDA path's data flow).  The
 # switches exist for tools/exp_bf16_parity.py, which attributes the end-to-end PSNR difference
 # against the FP32 oracle to weights / activations / gradients.
-ROUND = {"w": True, "act": True, "grad": True}
+ROUND = {"w": True, "act": True, "grad": True, "last": False}
+# "last": also round the 64->1 layer's operands (a_15 and its weights) -- NOT what the CUDA path does today (that layer
+# runs in FP32 on the CUDA cores); the switch exists to predict the parity cost of moving it to the tensor core.
 
 
 def bfw(t):
@@ -83,7 +85,9 @@ def forward_backward(flat, x, dy=None, running=None, train=True, residual=True):
         yk = zk * scale.view(1, -1, 1, 1) + shift.view(1, -1, 1, 1)
         z.append(zk)
         coef.append((scale, shift, mean, invstd, yk > 0))
-        a.append(bfa(F.relu(yk)) if k < 15 else F.relu(yk))   # the 64->1 layer consumes BN+ReLU of z_15 in FP32
+        a.append(bfa(F.relu(yk)) if (k < 15 or ROUND["last"]) else F.relu(yk))   # the 64->1 layer consumes BN+ReLU of z_15 in FP32
+    if ROUND["last"]:
+        w16 = bfw(w16)
     noise = F.conv2d(a[15], w16, padding=1)
     out = {"y": x - noise if residual else noise, "running": new_running}
     if dy is None:
