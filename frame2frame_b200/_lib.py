@@ -54,8 +54,6 @@ def _declare(lib):
     lib.f2f_dncnn_set_debug_dump.restype = None
     lib.f2f_dncnn_set_trace.argtypes = [vp]
     lib.f2f_dncnn_set_trace.restype = None
-    lib.f2f_dncnn_set_legacy.argtypes = [C.c_int]
-    lib.f2f_dncnn_set_legacy.restype = None
     lib.f2f_set_pdl.argtypes = [C.c_int]
     lib.f2f_set_pdl.restype = None
     lib.f2f_set_conv_pair.argtypes = [C.c_int]

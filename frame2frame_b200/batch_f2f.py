@@ -174,7 +174,7 @@ class BatchF2F:
         ws = net._ws_train.get(1, H, W, True, self.dev)
         sums = ws[self._stats_off:self._stats_off + NBN * 128 * 8].view(torch.float64).view(NBN, 2, NCH)
         b1, b2 = group["betas"]
-        stream = torch.cuda.current_stream().cuda_stream
+        stream = torch.cuda.current_stream(self.dev).cuda_stream
         P = net.flat_params.numel()
         n = len(self.local)
         stats_local = torch.empty((n, NBN, 2, NCH), dtype=torch.float32, device=self.dev)

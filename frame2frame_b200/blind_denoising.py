@@ -12,7 +12,8 @@ instead of once per iteration on the host, and nothing runs on the C
 
 ``OnlineF2F`` is the engine (frames and flows as tensors); ``blind_denoising()`` wraps it with
 the reference's file handling.  ``--flow`` may be omitted: the backward flow is then computed on
-the device by the TV-L1 kernels (what tvl1flow.sh:11-14 does in a separate process).
+the device by the TV-L1 kernels with the script's parameters (what tvl1flow.sh:11-14 does in a
+separate process: lambda 0.2, nscales 100 -> clamp, fscale 2; ``--flow_*`` flags override them).
 """
 import argparse
 import os
@@ -25,6 +26,7 @@ from ._lib import check, lib
 from .dncnn import Adam, DnCNN
 from .frame_io import OrderedSink, Prefetcher
 from .tvl1 import read_flo, tvl1flow
+from .tvl1flow_cli import SCRIPT_PARAMS
 from .warped_loss import WarpedLoss, warp_mask
 
 LR, WEIGHT_DECAY, BETAS, EPS = 5e-5, 0.00001, (0.9, 0.999), 1e-08   # blind_denoising.py:158-165
@@ -45,7 +47,11 @@ def load_network(model_fn, device):
         sd = {k: torch.from_numpy(np.asarray(v, dtype=np.float32 if v.dtype.kind == "f" else v.dtype))
               for k, v in np.load(model_fn).items()}
     else:
-        sd = torch.load(model_fn, map_location="cpu")
+        sd = torch.load(model_fn, map_location="cpu", weights_only=False)
+        if isinstance(sd, (list, tuple)):            # an --output_network file: torch.save([model, optimizer]), :258 / :148-151
+            sd = sd[0]
+        if isinstance(sd, nn.Module):
+            sd = sd.state_dict()
     if not any(k.startswith("module.") for k in sd):
         sd = {"module." + k: v for k, v in sd.items()}
     model.load_state_dict(sd)
@@ -81,8 +87,8 @@ class OnlineF2F:
         st, group = self.optimizer.fused_state(net)
         ws = net._ws_train.get(1, H, W, True, self.dev)
         b1, b2 = group["betas"]
-        stream = torch.cuda.current_stream().cuda_stream
         with torch.cuda.device(self.dev):
+            stream = torch.cuda.current_stream(self.dev).cuda_stream
             for _ in range(iters):
                 check(lib().f2f_step_train(net.flat_params.data_ptr(), net.flat_grads.data_ptr(), st["exp_avg"].data_ptr(),
                                            st["exp_avg_sq"].data_ptr(), net._running.data_ptr(), net._nbt.data_ptr(),
@@ -185,6 +191,9 @@ def _to_batch(im):
 def blind_denoising(**args):
     """Main function (blind_denoising.py:125-259).  args: the CLI parameters below."""
     dev = torch.device("cuda", int(args.get("gpu", 0) or 0))
+    # everything below (pinned-buffer copies, the `ready` events, the prefetch workers' pin_memory) acts on the CURRENT
+    # device and its current stream: make that this run's GPU, not cuda:0 (--gpu N, torchrun ranks with LOCAL_RANK >= 1)
+    torch.cuda.set_device(dev)
     model_fn = args["network"]
     if not os.path.isabs(model_fn):
         model_fn = os.path.join(os.path.abspath(os.path.dirname(__file__)), model_fn)
@@ -218,16 +227,21 @@ def blind_denoising(**args):
 
     lookahead = int(args.get("lookahead", 16) or 1)
     n = last - first + 1
+    # without --flow files the backward flows come from the device TV-L1 with the parameters the reference pipeline
+    # produces its .flo files with (tvl1flow.sh:11-18: lambda 0.2, nscales 100 -> clamp, fscale 2), unless overridden
+    flow_kw = dict(SCRIPT_PARAMS)
+    flow_kw.update({k[len("flow_"):]: v for k, v in args.items() if k.startswith("flow_") and v is not None})
     # decode ahead of the loop and encode/score behind it on host threads (frame_io.py); the loop itself never
     # waits on a PNG.  Each frame gets its own pinned result buffer, alive until the writer is done with it.
     with Prefetcher(read_frame, n, depth=lookahead + 2, workers=4) as frames, \
             Prefetcher(read_flow, n, depth=2, workers=1) as flow_files, OrderedSink(depth=8) as sink:
         flows = flow_files if args.get("flow") else None
-        for k, den in engine.run_sequence(frames, iters=args["iter"], lookahead=lookahead, flows=flows):
+        for k, den in engine.run_sequence(frames, iters=args["iter"], lookahead=lookahead, flows=flows, flow_kw=flow_kw):
             host = torch.empty(den.shape, dtype=den.dtype, pin_memory=True)
-            host.copy_(den, non_blocking=True)
-            ready = torch.cuda.Event()
-            ready.record()
+            with torch.cuda.device(dev):
+                host.copy_(den, non_blocking=True)
+                ready = torch.cuda.Event()
+                ready.record(torch.cuda.current_stream(dev))       # the stream the copy was enqueued on
             sink.submit(finish_frame, first + k, host, ready)
     torch.save([model, engine.optimizer], args["output_network"])
     plot_psnr.close()
@@ -293,6 +307,11 @@ def main(argv=None):
     parser.add_argument("--gpu", type=int, default=0, help="(added) CUDA device index")
     parser.add_argument("--align_corners", action="store_true", help="(added) sample with align_corners=True")
     parser.add_argument("--lookahead", type=int, default=16, help="(added) frame pairs per batched TV-L1 call when --flow is empty")
+    # (added) TV-L1 parameters of the on-device flow used when --flow is empty; defaults = tvl1flow/tvl1flow.sh:11-18
+    for name, typ in (("tau", float), ("lam", float), ("theta", float), ("nscales", int), ("fscale", int), ("zfactor", float),
+                      ("nwarps", int), ("epsilon", float)):
+        parser.add_argument("--flow_" + name, type=typ, default=None,
+                            help="(added) TV-L1 %s of the on-device flow (default %s, tvl1flow.sh)" % (name, SCRIPT_PARAMS[name]))
     argspar = parser.parse_args(argv)
     print("\n### Model-blind Video Denoising Via Frame-to-frame Training ###")
     print("> Parameters:")

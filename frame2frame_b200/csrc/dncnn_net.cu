@@ -741,17 +741,7 @@ struct Plan {
     int nz;
 };
 
-static int num_sms()
-{
-    static int sms = 0;
-    if (!sms) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        if (sms <= 0) sms = 148;
-    }
-    return sms;
-}
+static int num_sms() { return sm_count(); }   // of the current device (f2f_common.cuh)
 
 static Plan make_plan(int B, int H, int W, int train)
 {
@@ -772,7 +762,7 @@ static Plan make_plan(int B, int H, int W, int train)
     p.o_dw_small = take((size_t)1152 * 8);
     p.o_absmax = take(16);                         // bits of max|dy| (gradient scaling); zeroed by the same memset
     p.o_coef = take((size_t)NBN * C_STRIDE * 4);
-    p.o_partial = train ? take((size_t)148 * 2 * wg::PARTIAL * 4) : 0;
+    p.o_partial = train ? take((size_t)num_sms() * wg::PARTIAL * 4) : 0;   // one partial per CTA of the persistent grid
     p.total = o;
     return p;
 }
@@ -887,11 +877,7 @@ static int wgrad64_scaled(const void *d_act, const float *d_coef_in, void *d_g, 
         set_error("f2f_dncnn_wgrad64: bad arguments");
         return F2F_EINVAL;
     }
-    static bool configured = false;
-    if (!configured) {
-        F2F_CUDA_CHECK(cudaFuncSetAttribute(wg::k_wgrad64, cudaFuncAttributeMaxDynamicSharedMemorySize, wg::SMEM_BYTES));
-        configured = true;
-    }
+    F2F_CUDA_CHECK((ensure_dyn_smem<wg::k_wgrad64>(wg::SMEM_BYTES)));
     cudaStream_t st = (cudaStream_t)stream;
     wg::Args a;
     a.act = (const h16 *)d_act; a.coef_in = d_coef_in; a.g = (h16 *)d_g; a.z = (const h16 *)d_z; a.coef = d_coef;
@@ -923,12 +909,8 @@ int f2f_dncnn_backward(const float *d_params, float *d_grads, const float *d_dy,
         set_error("f2f_dncnn_backward: workspace too small (%zu bytes, need %zu)", ws_bytes, pl.total);
         return F2F_ENOMEM;
     }
-    static bool configured = false;
-    if (!configured) {
-        F2F_CUDA_CHECK(cudaFuncSetAttribute(rs::k_last_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, rs::SMEM));
-        F2F_CUDA_CHECK(cudaFuncSetAttribute(rs::k_first_wgrad, cudaFuncAttributeMaxDynamicSharedMemorySize, rs::SMEM));
-        configured = true;
-    }
+    F2F_CUDA_CHECK((ensure_dyn_smem<rs::k_last_bwd>(rs::SMEM)));
+    F2F_CUDA_CHECK((ensure_dyn_smem<rs::k_first_wgrad>(rs::SMEM)));
     cudaStream_t st = (cudaStream_t)stream;
     uint8_t *ws = (uint8_t *)d_ws;
     const size_t P = (size_t)H * W;

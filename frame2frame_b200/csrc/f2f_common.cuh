@@ -66,6 +66,26 @@ static inline cudaError_t launch_pdl_pairs(int big, void (*kernel)(KArgs...), di
     return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
 }
 
+// Multiprocessor count of the CURRENT device (cached per device ordinal; tvl1.cu).  Grids of the persistent kernels and
+// every buffer sized per CTA derive from it -- nothing assumes 148.
+int sm_count();
+
+// One-time opt-in to > 48 KB of dynamic shared memory for `Kernel` on the current device.  The attribute is per device
+// in CUDA, so the "done" state is a bit per device ordinal, not a process-wide flag (a second GPU in the same process
+// -- `--gpu 1`, BatchF2F tests across devices -- would otherwise launch unconfigured).
+template <auto Kernel>
+static inline cudaError_t ensure_dyn_smem(int bytes)
+{
+    static unsigned long long done = 0;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 64 && ((done >> dev) & 1ull)) return cudaSuccess;
+    e = cudaFuncSetAttribute(Kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e == cudaSuccess && dev < 64) done |= 1ull << dev;
+    return e;
+}
+
 static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 

@@ -213,7 +213,8 @@ int f2f_masked_loss(const float *d_in, const float *d_warped, const float *d_mas
     cudaStream_t st = (cudaStream_t)stream;
     k_zero_double<<<1, 1, 0, st>>>(d_loss);
     if (n) {
-        const int blocks = (int)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8);
+        const size_t cap = (size_t)sm_count() * 8;
+        const int blocks = (int)((n + 255) / 256 < cap ? (n + 255) / 256 : cap);
         const float inv_n = 1.0f / (float)n;
         if (kind == 0) k_masked_loss<0><<<blocks, 256, 0, st>>>(d_in, d_warped, d_mask, d_grad, d_loss, n, inv_n);
         if (kind == 1) k_masked_loss<1><<<blocks, 256, 0, st>>>(d_in, d_warped, d_mask, d_grad, d_loss, n, inv_n);

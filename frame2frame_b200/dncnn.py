@@ -231,19 +231,34 @@ class Adam(torch.optim.Optimizer):
             ptr += t.numel() * 4
         return True
 
+    def __setstate__(self, state):
+        # torch.optim.Optimizer.__getstate__ keeps defaults / state / param_groups only (torch.save([model, optimizer]),
+        # blind_denoising.py:258): the flat moment buffers are rebuilt from the per-parameter state on first use
+        super().__setstate__(state)
+        self.__dict__["_flat_state"] = {}
+
     def _flat_group_state(self, gi, ps):
         st = self._flat_state.get(gi)
         if st is None:
             n = sum(p.numel() for p in ps)
+            dev = ps[0].device
             st = self._flat_state[gi] = {
                 "step": 0,
-                "exp_avg": torch.zeros(n, dtype=torch.float32, device=ps[0].device),
-                "exp_avg_sq": torch.zeros(n, dtype=torch.float32, device=ps[0].device)}
+                "exp_avg": torch.zeros(n, dtype=torch.float32, device=dev),
+                "exp_avg_sq": torch.zeros(n, dtype=torch.float32, device=dev)}
             off = 0
             for p in ps:
                 k = p.numel()
-                self.state[p] = {"step": torch.tensor(0.0), "exp_avg": st["exp_avg"][off:off + k].view(p.shape),
-                                 "exp_avg_sq": st["exp_avg_sq"][off:off + k].view(p.shape)}
+                old = self.state.get(p) or {}
+                views = {"exp_avg": st["exp_avg"][off:off + k].view(p.shape),
+                         "exp_avg_sq": st["exp_avg_sq"][off:off + k].view(p.shape)}
+                step = torch.tensor(0.0)
+                if "exp_avg" in old:                  # resumed (unpickled / load_state_dict): keep the moments and the step
+                    views["exp_avg"].copy_(old["exp_avg"].to(dev))
+                    views["exp_avg_sq"].copy_(old["exp_avg_sq"].to(dev))
+                    step = torch.as_tensor(old.get("step", 0.0), dtype=torch.float32).cpu().clone()
+                    st["step"] = int(step.item())
+                self.state[p] = {"step": step, **views}
                 off += k
         return st
 

@@ -14,6 +14,16 @@
  *    the reference's C code; flows are planar (u1 plane then u2 plane), the
  *    layout main.c:173-174 allocates and `read_flow(...).permute(2,0,1)`
  *    (blind_denoising.py:206-209) produces.
+ *  - threading: calls act on the CURRENT CUDA device (cudaSetDevice) and are
+ *    serialised where they touch library-owned state: the TV-L1 entry points
+ *    hold one process-wide lock for the duration of a call (their cached staging
+ *    buffers, streams and convergence flags are shared and are rebuilt when the
+ *    current device changes), so concurrent callers are safe but do not overlap.
+ *    The DnCNN / F2F-step entry points keep no per-call state besides what the
+ *    caller passes in; the measurement and development switches
+ *    (f2f_profile_*, f2f_dncnn_set_trace / _set_debug_dump, f2f_set_*) are
+ *    process-global and must not be flipped while another thread is inside a call.
+ *    One host thread per GPU -- how torch.distributed runs it -- needs nothing else.
  *
  * Citations are into the reference tree (gauenk/frame2frame).
  */
@@ -219,7 +229,6 @@ void f2f_dncnn_set_debug_dump(void *d_buf);
 void f2f_dncnn_set_trace(unsigned long long *d_counters);
 /* Development aid: on != 0 routes the BN+ReLU-prologue convolutions to the older register-staged
  * kernel (dn::k_conv64) instead of the TMA-fed one with in-place transform warps, for comparison. */
-void f2f_dncnn_set_legacy(int on);
 /* Programmatic dependent launch of the per-layer DnCNN kernel chain: bit mask, default 3 (launch attribute on the big
  * and the small kernels, no early trigger); 0 launches the same kernels fully serialised (F2F_PDL in the environment
  * sets the initial value).  Results are identical, only the gaps between kernels differ (csrc/f2f_common.cuh). */

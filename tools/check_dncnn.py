@@ -49,7 +49,7 @@ def check_wgrad(H, W):
         g_nhwc = g.permute(0, 2, 3, 1).contiguous()
         zp_nhwc = z_prev.permute(0, 2, 3, 1).contiguous()
         z_nhwc = z.permute(0, 2, 3, 1).contiguous()
-        partial = torch.zeros(148 * 49152, device=dev)
+        partial = torch.zeros(torch.cuda.get_device_properties(dev).multi_processor_count * 49152, device=dev)
         dw = torch.full((64, 64, 3, 3), float("nan"), device=dev)
         _lib.check(lib.f2f_dncnn_wgrad64(zp_nhwc.data_ptr(),
                                          coef_in.data_ptr() if bn_in else None, g_nhwc.data_ptr(),

@@ -27,16 +27,8 @@ def dgrad(bn):
                                          zeros.data_ptr() if bn else None, ones.data_ptr() if bn else None,
                                          st.data_ptr() if bn else None, H, W, None)
 names = ["prod wait", "prod work", "mma w.acc", "mma w.tile", "mma issue", "epi wait", "epi work", "epi total", "tiles"]
-def legacy(fn):
-    def run():
-        lib.f2f_dncnn_set_legacy(1)
-        r = fn()
-        lib.f2f_dncnn_set_legacy(0)
-        return r
-    return run
 for name, fn in [("conv raw/store", conv(0, 0)), ("conv raw/stats", conv(0, 1)), ("conv bn/store", conv(1, 0)),
-                 ("conv bn/stats", conv(1, 1)), ("legacy bn/store", legacy(conv(1, 0))), ("legacy bn/stats", legacy(conv(1, 1))),
-                 ("dgrad relu", dgrad(0)), ("dgrad bn", dgrad(1))]:
+                 ("conv bn/stats", conv(1, 1)), ("dgrad relu", dgrad(0)), ("dgrad bn", dgrad(1))]:
     for _ in range(2):
         fn()
     e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
