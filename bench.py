@@ -33,11 +33,15 @@ sys.path.insert(0, ROOT)
 
 H, W = 1080, 1920
 NSCALES = 5
-PAIRS_PER_STEP = 16          # per GPU; 16 pairs x 2 frames x 8.3 MB = 265 MB > L2 (126 MB)
+NSLOTS = 16                  # frame pairs advancing in lock-step on a GPU (one "group")
+PAIRS_PER_STEP = 32          # per GPU: two groups, so that the host-buffer call's upload / solve / download pipeline
+                             # (f2f_tvl1_flow_batch_host double-buffers successive groups of ONE call) is exercised;
+                             # 32 pairs x 2 frames x 8.3 MB = 531 MB > L2 (126 MB)
 ALG_BYTES_PER_PX_ITER = 64   # read rho_c,I1wx,I1wy,grad,u1,u2,p11..p22; write u1,u2,p11..p22
 
 
 from frame2frame_b200.benchutil import ClockSampler, peaks  # noqa: E402
+import bench_f2f  # noqa: E402
 
 
 _REAL_STDOUT = None
@@ -159,11 +163,11 @@ def ours_tvl1(args, rank, world, local_rank, with_cpu=True):
         torch.cuda.synchronize()
 
     def step_device():
-        return tvl1flow(dI0, dI1, nslots=n, nscales=NSCALES)
+        return tvl1flow(dI0, dI1, nslots=NSLOTS, nscales=NSCALES)
 
     def step_host():
         _lib.check(lib.f2f_tvl1_flow_batch_host(pI0.data_ptr(), pI1.data_ptr(), pU.data_ptr(), n, W, H, C.byref(p),
-                                                None, n), "f2f_tvl1_flow_batch_host")
+                                                None, NSLOTS), "f2f_tvl1_flow_batch_host")
 
     # ---- device-resident timing (`value`) ----
     for _ in range(args.warmup):
@@ -216,8 +220,8 @@ def ours_tvl1(args, rank, world, local_rank, with_cpu=True):
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": "configs[1]: tvl1flow on synthetic 1080p gray frame pairs, 5-scale pyramid, 5 warps, "
                                "eps 0.01, frame pairs sharded over GPUs",
-                   "pairs_per_step_per_gpu": n, "frame": "%dx%d" % (W, H),
-                   "l2": "inputs larger than L2 (265 MB of frames + 3.4 GB of solver state per step)"},
+                   "pairs_per_step_per_gpu": n, "pairs_in_lock_step": NSLOTS, "frame": "%dx%d" % (W, H),
+                   "l2": "inputs larger than L2 (531 MB of frames + 3.4 GB of solver state per step)"},
         "e2e": {"value": e2e_value, "unit": "fields/s", "h2d_bytes_per_step": 2 * n * H * W * 4,
                 "d2h_bytes_per_step": 2 * n * H * W * 4, "api": "f2f_tvl1_flow_batch_host (C ABI, pinned host buffers)",
                 "flow_abs_mean": checksum},
@@ -231,8 +235,7 @@ def ours_tvl1(args, rank, world, local_rank, with_cpu=True):
                      "px_iters_per_step": px0 * slot_iters0 / args.steps,
                      "launches_per_step": launches0 / args.steps,
                      "avg_launch_us": iter_ms * 1e3 / launches0 if launches0 else None,
-                     "traffic": 2.148e9, "traffic_note": "dram read+write per launch of 16 slots, ncu --set full, "
-                                                         "profiles/r01_ncu_tvl1_iter_strip.txt"},
+                     "traffic": bench_f2f._traffic("k_iter_strip")[0], "traffic_source": bench_f2f._traffic("k_iter_strip")[1]},
     }
     if world == 1 and not args.no_cpu and with_cpu:
         line["cpu_baseline"] = cpu_baseline()
@@ -248,11 +251,12 @@ def main():
     ap.add_argument("--workload", default="f2f", choices=["f2f", "tvl1", "batch"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-tvl1", action="store_true", help="f2f workload: skip the secondary TV-L1 measurement")
+    ap.add_argument("--no-batch", action="store_true", help="f2f workload: skip the secondary batch-mode (NCCL) measurement")
+    ap.add_argument("--no-config0", action="store_true", help="reference arm: skip the non-extrapolated configs[0] point")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    import bench_f2f
     # stdout carries the JSON line and nothing else: libraries that write to file descriptor 1 on their own (NCCL's
     # version banner under torchrun) are sent to stderr for the duration of the run
     quiet_stdout()
@@ -277,14 +281,22 @@ def main():
             line = bench_f2f.ours_batch(args, rank, world, local_rank, ClockSampler, peaks)
         else:
             line = bench_f2f.ours(args, rank, world, local_rank, ClockSampler, peaks)
+            keys = ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "scaling", "config", "e2e", "roofline",
+                    "cpu_baseline", "clocks", "gpu_launches")
             if not args.no_tvl1:
-                # the metric's second half (TV-L1 flow fields/sec, configs[1]) as a short secondary measurement
+                # the metric's second half (TV-L1 flow fields/sec, configs[1]) at every N, >= 5 timed steps
                 targs = argparse.Namespace(**vars(args))
-                targs.steps, targs.warmup = 2, 3
+                targs.steps, targs.warmup = max(5, min(args.steps, 8)), 3
                 t = ours_tvl1(targs, rank, world, local_rank, with_cpu=True)
                 if rank == 0:
-                    line["tvl1"] = {k: t[k] for k in ("metric", "value", "unit", "ms_per_step", "config", "e2e", "roofline",
-                                                      "cpu_baseline") if k in t}
+                    line["tvl1"] = {k: t[k] for k in keys if k in t}
+            if not args.no_batch:
+                # configs[3]: batch-mode fine-tune with the NCCL gradient all-reduce (the one path with a collective)
+                bargs = argparse.Namespace(**vars(args))
+                bargs.steps, bargs.warmup = 5, 2
+                t = bench_f2f.ours_batch(bargs, rank, world, local_rank, ClockSampler, peaks)
+                if rank == 0:
+                    line["batch"] = {k: t[k] for k in keys + ("model_tflops_per_gpu", "comm") if k in t}
         if rank == 0:
             emit(line)
     finally:

@@ -83,45 +83,139 @@ def _oracle_flow_seconds(cores):
     return time.perf_counter() - t0
 
 
+def workload_config():
+    """`config` of BOTH arms (the driver compares them): the workload, nothing about how an arm computes it."""
+    return {"workload": "configs[2]: online F2F denoise, 1080p gray sigma=25 synthetic seq, DnCNN-25 layout (weights pre-trained on "
+                        "synthetic textures: tests/golden/dncnn_s25_synth.npz), iter=20 per frame, TV-L1 backward flow of every "
+                        "frame pair (5 scales, 5 warps, main.c defaults) computed inside the timed region; 1 frame per step per "
+                        "GPU, ranks denoise independent chunks (no collective)",
+            "frame": "%dx%d" % (W, H), "iter": ITERS,
+            "l2": "inputs larger than L2: every layer streams 265 MB activations (4.8 GB workspace per step)"}
+
+
+def _sample(torch, cores):
+    """One bounded sample of a frame's work on the host cores: 1 fine-tuning iteration + 1 eval forward + the TV-L1 flow.
+    -> (seconds measured, seconds per frame extrapolated linearly to iter = ITERS, parts)"""
+    t_it, t_ev = _oracle_frame_seconds(torch, cores, 1)
+    t_fl = _oracle_flow_seconds(cores)
+    return t_it + t_ev + t_fl, ITERS * t_it + t_ev + t_fl, (t_it, t_ev, t_fl)
+
+
 def cpu_baseline():
     import torch
     cores = os.cpu_count() or 1
-    t_it, t_ev = _oracle_frame_seconds(torch, cores, 1)
-    t_fl = _oracle_flow_seconds(cores)
-    sec = ITERS * t_it + t_ev + t_fl
-    return {"value": 1.0 / sec, "unit": "frames/s", "cores": cores, "kind": "port",
+    meas, frame, (t_it, t_ev, t_fl) = _sample(torch, cores)
+    return {"value": 1.0 / frame, "unit": "frames/s", "cores": cores, "kind": "port",
             "sample": "1 fine-tuning iteration (%.1f s) + 1 eval forward (%.1f s) + the TV-L1 flow (%.1f s, tvl1flow_lib.c) of "
                       "one 1920x1080 frame, torch %s CPU FP32 %d threads; extrapolated to iter=20 per frame"
                       % (t_it, t_ev, t_fl, torch.__version__, cores)}
 
 
+C0_H, C0_W, C0_FRAMES = 540, 960, 2      # BASELINE.json configs[0] (the reference's own CPU-runnable case), first frames
+
+
+def config0_reference(torch, cores):
+    """A NON-extrapolated reference point: the FP32 CPU loop on the first C0_FRAMES frames of configs[0] (960x540,
+    analytic flows, iter = 20 each, eval forward, PSNR) -- every iteration really runs.  -> dict"""
+    import numpy as np
+    from frame2frame_b200 import synth
+    from frame2frame_b200.blind_denoising import psnr
+    from oracle import dncnn_oracle as do
+    torch.set_num_threads(cores)
+    model = do.load_numpy_state(do.OracleDnCNN(residual=False), synth.pretrained_state_dict())
+    opt = do.make_adam(model)
+    fr = [synth.noisy_frame(C0_H, C0_W, t) / np.float32(255.0) for t in range(C0_FRAMES + 1)]
+    t0 = time.perf_counter()
+    ps = []
+    for t in range(1, C0_FRAMES + 1):
+        den = do.finetune_frame(model, opt, fr[t], fr[t - 1], synth.backward_flow(C0_H, C0_W, t), ITERS)
+        ps.append(float(psnr(synth.clean_frame_u8(C0_H, C0_W, t) / np.float32(255.0), den)))
+    dt = time.perf_counter() - t0
+    return {"workload": "configs[0]: %d frames 960x540, analytic flows, iter=20, every iteration executed (no extrapolation)" % C0_FRAMES,
+            "value": C0_FRAMES / dt, "unit": "frames/s", "seconds": dt, "cores": cores, "psnr_db": ps}
+
+
 def reference_arm(args, rank, world):
+    """The reference's CPU loop on the host cores.  A step = ONE bounded sample of a frame's work (1 iteration + 1 eval
+    forward + the flow); `ms_per_step` is that measured time, `value` the frames/s it implies for iter = 20
+    (`extrapolation` says how), so steps x ms_per_step is what this run really took."""
     if rank != 0:
         return
     import torch
     cores = os.cpu_count() or 1
     for _ in range(min(args.warmup, 1)):
-        _oracle_frame_seconds(torch, cores, 1)
-    t_it = t_ev = t_fl = 0.0
+        _sample(torch, cores)
+    meas = frame = 0.0
+    parts = [0.0, 0.0, 0.0]
     for _ in range(args.steps):
-        a, b = _oracle_frame_seconds(torch, cores, 1)
-        t_it += a
-        t_ev += b
-        t_fl += _oracle_flow_seconds(cores)
-    sec = (ITERS * t_it + t_ev + t_fl) / args.steps
-    v = 1.0 / sec
-    emit({
+        m, f, p = _sample(torch, cores)
+        meas += m
+        frame += f
+        parts = [a + b for a, b in zip(parts, p)]
+    meas, frame = meas / args.steps, frame / args.steps
+    parts = [v / args.steps for v in parts]
+    v = 1.0 / frame
+    line = {
         "impl": "reference", "metric": METRIC, "value": v, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "configs[2]: online F2F denoise, 1080p gray sigma=25 synthetic seq, DnCNN-25, iter=20 per frame "
-                               "(bounded sample per step: 1 fine-tuning iteration + 1 eval forward + the frame's TV-L1 flow, extrapolated to iter=20)"},
+        "warmup": args.warmup, "ms_per_step": meas * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "config": workload_config(),
+        "extrapolation": {"frame_ms": frame * 1e3, "formula": "iter * t_iteration + t_eval + t_flow", "iter": ITERS,
+                          "t_iteration_s": parts[0], "t_eval_s": parts[1], "t_flow_s": parts[2],
+                          "note": "value = 1000 / frame_ms; ms_per_step is the measured sample (1 iteration + eval + flow)"},
         "cpu_baseline": {"value": v, "unit": "frames/s", "cores": cores, "kind": "port",
                          "sample": "%d x (1 iteration + 1 eval forward + TV-L1 flow) of a 1920x1080 frame, torch CPU FP32 %d threads; the "
                                    "reference's DnCNN submodule is un-vendored, so its loop is restated with the same stock "
-                                   "torch modules (oracle/dncnn_oracle.py)" % (args.steps, cores)},
+                                   "torch modules (oracle/dncnn_oracle.py); flow by the reference's tvl1flow_lib.c (oracle/_ref)"
+                                   % (args.steps, cores)},
         "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    })
+    }
+    if args.gpus == 1 and not getattr(args, "no_config0", False):
+        line["config0"] = config0_reference(torch, cores)
+    emit(line)
+
+
+def _traffic(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel`, from the committed ncu --set full summary
+    (profiles/r02_traffic.json, written by tools/ncu_summary.py from the .ncu-rep) -- None when no capture is committed."""
+    fn = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r02_traffic.json")
+    try:
+        d = json.load(open(fn))
+        return d.get(kernel), "profiles/r02_traffic.json (%s)" % d.get("source", "ncu --set full")
+    except Exception:
+        return None, "no ncu --set full capture committed for this kernel"
+
+
+def _golden(name):
+    try:
+        return json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "tests", "golden", name)))
+    except Exception:
+        return None
+
+
+def parity_leg(torch, dev, gold, nframes):
+    """The CUDA loop from the pretrained weights on the first frames of a committed FP32-oracle record (analytic
+    flows): per-frame PSNR difference against it, and the device time per frame.  Not part of any timed region."""
+    import numpy as np
+    from frame2frame_b200 import synth
+    from frame2frame_b200.blind_denoising import OnlineF2F, load_network, psnr
+    w, h = (int(v) for v in gold["frame"].split("x"))
+    n = min(nframes, len(gold["frames"]))
+    fixture = os.path.join(os.path.dirname(os.path.abspath(__file__)), "tests", "golden", "dncnn_s25_synth.npz")
+    eng = OnlineF2F(load_network(fixture, dev))
+    host = [torch.from_numpy(synth.noisy_frame(h, w, t) / np.float32(255.0))[None, None].pin_memory() for t in range(n + 1)]
+    flows = {t: torch.from_numpy(synth.backward_flow(h, w, t))[None].to(dev) for t in range(1, n + 1)}
+    outs = [torch.empty((1, 1, h, w), dtype=torch.float32).pin_memory() for _ in range(n + 1)]
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in eng.run_sequence(host, gold["iters"], flows=flows, out=outs):
+        pass
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    d = []
+    for t in range(1, n + 1):
+        clean = synth.clean_frame_u8(h, w, t) / np.float32(255.0)
+        d.append(float(psnr(clean, outs[t][0, 0].numpy())) - gold["frames"][t - 1]["psnr_oracle"])
+    return d, n / dt
 
 
 def ours(args, rank, world, local_rank, ClockSampler, peaks):
@@ -165,23 +259,20 @@ def ours(args, rank, world, local_rank, ClockSampler, peaks):
             pass
         torch.cuda.current_stream().synchronize()
 
+    # ---- `value`: frames resident in HBM, no instrumentation inside the timed region ----
     run_device(0, args.warmup)
     prof = (C.c_double * 5)()
     lib.f2f_profile_read(prof)
     launches_before = prof[4]
-    lib.f2f_profile_dncnn(1)
     barrier()
     sampler = ClockSampler(local_rank) if rank == 0 else None
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    den = run_device(args.warmup, args.steps)
+    run_device(args.warmup, args.steps)
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1)
     clocks = sampler.stop() if sampler else None
-    dn = (C.c_double * 4)()
-    lib.f2f_profile_dncnn_read(dn)
-    lib.f2f_profile_dncnn(0)
     lib.f2f_profile_read(prof)
     launches = prof[4] - launches_before
     t = torch.tensor([ms], dtype=torch.float64, device=dev)
@@ -190,7 +281,7 @@ def ours(args, rank, world, local_rank, ClockSampler, peaks):
     ms_max = float(t.item())
     value = world * args.steps / (ms_max * 1e-3)
 
-    # ---- end to end: host frames in, denoised frame out, through OnlineF2F.step_frame ----
+    # ---- `e2e`: host frames in, denoised frames out, through OnlineF2F.run_sequence ----
     run_host(0, 1)
     barrier()
     t0 = time.perf_counter()
@@ -204,6 +295,22 @@ def ours(args, rank, world, local_rank, ClockSampler, peaks):
     kk = (1 + args.steps) % nf
     quality = psnr(synth.clean_frame_u8(H, W, kk) / np.float32(255.0), out_host[0, 0].numpy())
 
+    # ---- roofline: per-launch CUDA events around every 64->64 convolution / weight-gradient launch, in a SEPARATE pass
+    # of the same loop after the timed regions (the event records sit between the PDL-chained launches, so they must
+    # not be inside `value`) ----
+    psteps = min(args.steps, 3)
+    lib.f2f_profile_dncnn(1)
+    torch.cuda.synchronize()
+    p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    p0.record()
+    run_device(args.warmup + args.steps, psteps)
+    p1.record()
+    torch.cuda.synchronize()
+    pms = p0.elapsed_time(p1)
+    dn = (C.c_double * 4)()
+    lib.f2f_profile_dncnn_read(dn)
+    lib.f2f_profile_dncnn(0)
+
     if rank != 0:
         return
     pk, pk_kind = peaks()
@@ -213,18 +320,15 @@ def ours(args, rank, world, local_rank, ClockSampler, peaks):
     wg_tf = CONV64_FLOP_PER_PX * P * wg_n / (wg_ms * 1e-3) / 1e12 if wg_ms > 0 else None
     peak_tf = pk.get("bf16_tflops_sustained", pk["bf16_tflops"])
     frame_flop = (ITERS * FLOP_PER_PX_TRAIN + FLOP_PER_PX_FWD) * P
+    traffic, traffic_src = _traffic("k_conv64t")
+    wg_traffic, _ = _traffic("k_wgrad64")
+    mode = h16.upper() + " operands/activations/gradients, FP32 accumulate, FP32 master weights, Adam and BatchNorm statistics"
     line = {
         "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": h16, "data": "synthetic",
-        "config": {"workload": "configs[2]: online F2F denoise, 1080p gray sigma=25 synthetic seq, DnCNN-25 layout "
-                               "(weights pre-trained on synthetic textures: tests/golden/dncnn_s25_synth.npz), iter=20 per "
-                               "frame, TV-L1 backward flows computed on the device inside the timed region (up to %d consecutive "
-                               "pairs per batched call); 1 frame per step per GPU, " % LOOKAHEAD +
-                               "ranks denoise independent chunks (no collective)",
-                   "frame": "%dx%d" % (W, H), "iter": ITERS, "precision": h16.upper() + " operands/activations/gradients, FP32 accumulate, "
-                   "FP32 master weights, Adam and BatchNorm statistics",
-                   "l2": "inputs larger than L2: every layer streams 265 MB activations (4.8 GB workspace per step)"},
+        "dtype": h16, "data": "synthetic", "config": workload_config(),
+        "mode": {"name": h16, "precision": mode,
+                 "note": "the mode that produced `value`, `e2e` and `psnr_delta_db`; see DESIGN.md section 2 for its parity record"},
         "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": H * W * 4, "d2h_bytes_per_step": H * W * 4,
                 "api": "OnlineF2F.run_sequence (frame2frame_b200/blind_denoising.py) from/to pinned host frames; "
                        "(steps+1)/steps frames uploaded per step (the first frame of the run is only a `prev`)",
@@ -232,21 +336,30 @@ def ours(args, rank, world, local_rank, ClockSampler, peaks):
         "gpu_launches": int(launches),
         "clocks": clocks,
         "model_tflops": frame_flop * value / world / 1e12,
-        "roofline": {"bound": "tensor", "kernel": "k_conv64 / k_conv64t (tcgen05 implicit-GEMM 3x3 64->64 conv: the forward and "
+        "mfu": frame_flop * value / world / 1e12 / peak_tf,
+        "roofline": {"bound": "tensor", "kernel": "dnt::k_conv64t (tcgen05 implicit-GEMM 3x3 64->64 conv: the forward and "
                                                   "input-gradient launches)",
                      "achieved": conv_tf, "peak": peak_tf, "peak_source": pk_kind + " bf16_tflops_sustained", "unit": "TFLOP/s",
                      "frac": conv_tf / peak_tf if conv_tf else None, "flop_per_launch": CONV64_FLOP_PER_PX * P,
-                     "launches_per_step": conv_n / args.steps, "avg_launch_us": conv_ms * 1e3 / conv_n if conv_n else None,
-                     "share_of_step": conv_ms / ms if ms else None,
+                     "launches_per_step": conv_n / psteps, "avg_launch_us": conv_ms * 1e3 / conv_n if conv_n else None,
+                     "share_of_step": conv_ms / pms if pms else None,
+                     "measured": "CUDA events around every launch, %d steps of the same loop run after the timed regions" % psteps,
                      "wgrad64": {"achieved": wg_tf, "frac": wg_tf / peak_tf if wg_tf else None,
-                                 "avg_launch_us": wg_ms * 1e3 / wg_n if wg_n else None, "share_of_step": wg_ms / ms if ms else None},
-                     # dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full (profiles/r01_ncu_conv64_wgrad64.txt):
-                     # forward k_conv64t<1,1> 266 + 218 MB, input gradient k_conv64t<0,2> 531 + 235 MB (algorithmic 531 / 796 MB;
-                     # the writes still dirty in the 126 MB L2 at kernel end are not counted by ncu); mean over the 15 + 15 launches
-                     "traffic": 625e6,
-                     "traffic_note": "mean of forward (484 MB) and input-gradient (766 MB) launches, ncu --set full, "
-                                     "profiles/r01_ncu_conv64_wgrad64.txt; wgrad64 1041 MB (algorithmic 1061 MB)"},
+                                 "avg_launch_us": wg_ms * 1e3 / wg_n if wg_n else None, "share_of_step": wg_ms / pms if pms else None,
+                                 "traffic": wg_traffic},
+                     "traffic": traffic, "traffic_source": traffic_src},
     }
+    # ---- parity against the committed FP32-oracle records (outside every timed region) ----
+    g1080, g0 = _golden("f2f_1080p_ref.json"), _golden("f2f_config0_ref.json")
+    if g1080 is not None:
+        d, _ = parity_leg(torch, dev, g1080, 2)
+        line["psnr_delta_db"] = {"vs": "tests/golden/f2f_1080p_ref.json (FP32 CPU oracle loop, 1920x1080, analytic flows)",
+                                 "per_frame": d, "max_abs": float(np.max(np.abs(d))), "mode": h16}
+    if world == 1 and g0 is not None:
+        d, fps = parity_leg(torch, dev, g0, C0_FRAMES)
+        line["config0"] = {"workload": "configs[0]: %d frames 960x540, analytic flows, iter=20, from/to pinned host frames" % C0_FRAMES,
+                           "value": fps, "unit": "frames/s", "psnr_delta_db": d,
+                           "note": "the reference arm times the same frames on the host cores without extrapolation (its `config0`)"}
     if world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline()
     return line
@@ -353,6 +466,9 @@ def ours_batch(args, rank, world, local_rank, ClockSampler, peaks):
                 "d2h_bytes_per_step": NSEQ * H * W * 4,
                 "api": "BatchF2F.finetune + denoise (frame2frame_b200/batch_f2f.py) from/to pinned host frames"},
         "gpu_launches": int(launches),
+        "comm": {"backend": "nccl" if world > 1 else "none (one rank)", "ranks": world,
+                 "per_inner_iteration": "one all-reduce(SUM) of the flat 556032-float gradient + one all-gather of 1920 BatchNorm "
+                                        "statistics per local sequence, issued after the backward pass of the last local sequence"},
         "roofline": {"bound": "tensor", "kernel": "whole train step (model FLOPs)", "achieved": tf, "peak": peak_tf,
                      "peak_source": pk_kind + " bf16_tflops_sustained", "unit": "TFLOP/s", "frac": tf / peak_tf, "traffic": None},
     }

@@ -98,6 +98,6 @@ def pretrained_state_dict(path=None):
     as float32 numpy arrays."""
     import os
     if path is None:
-        path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden",
+        path = os.environ.get("F2F_PRETRAINED") or os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden",
                             "dncnn_s25_synth.npz")
     return {k: (np.asarray(v, np.float32) if v.dtype.kind == "f" else np.asarray(v)) for k, v in np.load(path).items()}

@@ -289,6 +289,7 @@ void f2f_profile_dncnn_read(double out[4]);
  * *h_mismatches receives the number of differing results (expected 0). */
 int f2f_selftest_division(unsigned long long n, unsigned long long *h_mismatches);
 
+
 /* Release every cached device allocation of the calling process. */
 void f2f_release(void);
 

@@ -5,8 +5,8 @@
   * two processes sharing the work (sequences sharded, gradient exchange, ordered BatchNorm EMA)
     give BIT-IDENTICAL weights, running statistics and outputs to the one-process run in
     deterministic mode, and agree to float association in all-reduce mode.
-The two-rank runs use the gloo backend on CUDA tensors of one device so they need a single GPU;
-the NCCL path is exercised by `bench.py --workload batch --gpus N`."""
+The gloo two-rank runs work on CUDA tensors of one device so they need a single GPU; the NCCL two-rank
+run (one process per GPU, the production configuration) needs two and is skipped on a one-GPU box."""
 import os
 import socket
 
@@ -32,7 +32,7 @@ def _inputs():
 def _net(dev):
     from frame2frame_b200 import synth
     from frame2frame_b200.dncnn import DnCNN
-    net = torch.nn.DataParallel(DnCNN(residual=False), device_ids=[0]).to(dev)
+    net = torch.nn.DataParallel(DnCNN(residual=False), device_ids=[dev.index or 0]).to(dev)
     net.load_state_dict({k: torch.from_numpy(v) for k, v in synth.pretrained_state_dict().items()})
     return net
 
@@ -58,6 +58,19 @@ def _worker(rank, world, port, deterministic, out_dir):
     try:
         p, r, d, l = _run(torch.device("cuda:0"), world, rank, deterministic)
         np.savez(os.path.join(out_dir, "r%d.npz" % rank), p=p, r=r, d=d, l=l)
+    finally:
+        dist.destroy_process_group()
+
+
+def _worker_nccl(rank, world, port, deterministic, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dev = torch.device("cuda", rank)
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        p, r, d, l = _run(dev, world, rank, deterministic)
+        np.savez(os.path.join(out_dir, "n%d.npz" % rank), p=p, r=r, d=d, l=l)
     finally:
         dist.destroy_process_group()
 
@@ -116,3 +129,24 @@ def test_two_ranks_equal_one(cuda, tmp_path, deterministic):
             assert np.allclose(z["r"], r1, rtol=1e-4, atol=1e-6)
     a, b = (np.load(os.path.join(str(tmp_path), "r%d.npz" % k)) for k in range(2))
     assert np.array_equal(a["p"], b["p"])                          # ranks hold identical weights afterwards
+
+
+@pytest.mark.parametrize("deterministic", [True, False])
+def test_two_ranks_nccl_equal_one(cuda, tmp_path, deterministic):
+    """The production exchange: one process per GPU, gradients and BatchNorm statistics over NCCL
+    (batch_f2f.exchange_gradients / gather_rows take the CUDA tensors as they are).  Deterministic mode must be
+    bit-identical to the one-rank run; all-reduce mode agrees to float association."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs (NCCL, one process per GPU)")
+    p1, r1, d1, l1 = _run(cuda, 1, 0, deterministic)
+    mp.spawn(_worker_nccl, args=(2, _free_port(), deterministic, str(tmp_path)), nprocs=2, join=True)
+    a, b = (np.load(os.path.join(str(tmp_path), "n%d.npz" % k)) for k in range(2))
+    assert np.array_equal(a["p"], b["p"]) and np.array_equal(a["r"], b["r"])
+    for z in (a, b):
+        if deterministic:
+            assert np.array_equal(z["p"], p1) and np.array_equal(z["r"], r1) and np.array_equal(z["l"], l1)
+        else:
+            assert np.allclose(z["l"], l1, rtol=1e-6)
+            assert np.abs(z["p"] - p1).max() <= 1e-4
+            assert np.allclose(z["r"], r1, rtol=1e-4, atol=1e-6)
+    assert np.array_equal(a["d"], d1) if deterministic else np.allclose(a["d"], d1, atol=1e-3)

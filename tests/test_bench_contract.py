@@ -67,3 +67,26 @@ def test_peaks_fall_back_when_the_driver_file_is_absent(tmp_path, monkeypatch):
     (tmp_path / "MEASURED_PEAKS.json").write_text('{"hbm_gbs": 6551.7, "bf16_tflops": 1630.0, "bf16_tflops_sustained": 1385.1}')
     pk, kind = benchutil.peaks()
     assert kind == "measured" and pk["hbm_gbs"] == 6551.7
+
+
+def test_f2f_reference_arm_reports_the_measured_sample():
+    """The headline workload's reference arm: `ms_per_step` is the time of the bounded sample it really ran (so that
+    steps x ms_per_step fits the run), `value` the frames/s extrapolated to iter = 20 with the extrapolation spelled out,
+    and `config` is the very dict our own arm prints (the driver compares them)."""
+    import time
+    import bench_f2f
+    t0 = time.time()
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0",
+                        "--no-config0"], capture_output=True, text=True, timeout=900, cwd=ROOT)
+    wall = time.time() - t0
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [l for l in r.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["unit"] == "frames/s" and d["metric"] == bench_f2f.METRIC
+    assert d["config"] == bench_f2f.workload_config()
+    assert d["steps"] * d["ms_per_step"] * 1e-3 <= wall                      # the sample really is what was timed
+    ex = d["extrapolation"]
+    assert abs(ex["frame_ms"] - 1e3 * (ex["iter"] * ex["t_iteration_s"] + ex["t_eval_s"] + ex["t_flow_s"])) < 1.0
+    assert abs(d["value"] - 1e3 / ex["frame_ms"]) < 1e-9 and d["ms_per_step"] < ex["frame_ms"]
+    assert d["e2e"]["value"] == d["value"] and d["cpu_baseline"]["cores"] == (os.cpu_count() or 1)

@@ -273,6 +273,62 @@ def test_blind_denoising_cli(cuda, tmp_path):
     assert np.allclose(res["files"], res["tvl1"], atol=1.0)
 
 
+def test_cli_on_second_gpu_equals_first(cuda, tmp_path):
+    """`--gpu 1` must give what `--gpu 0` gives (the result copy and its `ready` event used to go to
+    different devices' streams, so the writer thread could encode a pinned buffer the copy had not reached yet).
+    960x540 frames so that the D2H copy is long enough to lose that race; BatchNorm sums are FP64 atomics (order
+    varies run to run), hence a tolerance of one grey level / 1e-3 dB instead of bit equality."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    from PIL import Image
+    from frame2frame_b200 import blind_denoising as bd, synth
+    H, W, NF = 540, 960, 3
+    torch.save({k: torch.from_numpy(v) for k, v in synth.pretrained_state_dict().items()}, str(tmp_path / "net.pth"))
+    for t in range(NF + 1):
+        Image.fromarray(synth.noisy_frame(H, W, t).astype(np.uint8)).save(str(tmp_path / ("in_%03d.png" % t)))
+        Image.fromarray(synth.clean_frame_u8(H, W, t).astype(np.uint8)).save(str(tmp_path / ("ref_%03d.png" % t)))
+    res = {}
+    for gpu in (0, 1):
+        out = tmp_path / ("gpu%d" % gpu)
+        out.mkdir()
+        bd.main(["--input", str(tmp_path / "in_%03d.png"), "--ref", str(tmp_path / "ref_%03d.png"), "--first", "0", "--last", str(NF),
+                 "--iter", "3", "--network", str(tmp_path / "net.pth"), "--gpu", str(gpu), "--flow_nscales", "4",
+                 "--output", str(out / "%03d.png"), "--output_psnr", str(out / "psnr.txt"), "--output_network", str(out / "final.pth")])
+        res[gpu] = ([float(l) for l in open(out / "psnr.txt").read().split()],
+                    [np.array(Image.open(out / ("%03d.png" % t))).astype(np.int32) for t in range(1, NF + 1)])
+    torch.cuda.set_device(0)
+    assert np.allclose(res[0][0], res[1][0], atol=1e-3), (res[0][0], res[1][0])
+    for a, b in zip(res[0][1], res[1][1]):
+        assert np.abs(a - b).max() <= 1
+
+
+def test_checkpoint_resume_round_trip(cuda, tmp_path):
+    """torch.save([model, optimizer]) (blind_denoising.py:258) -> torch.load -> keep training: the reloaded pair must
+    continue exactly like the pair that was never saved (flat Adam moments and step count rebuilt from the pickled
+    per-parameter state), and load_network() must accept such a file as --network (blind_denoising.py:148-151)."""
+    from frame2frame_b200 import synth
+    from frame2frame_b200.blind_denoising import OnlineF2F, load_network
+    H, W = 48, 64
+    fr = [torch.from_numpy(synth.noisy_frame(H, W, t) / np.float32(255.0))[None, None] for t in range(3)]
+    fl = [None] + [torch.from_numpy(synth.backward_flow(H, W, t))[None] for t in (1, 2)]
+    net, _ = _models(cuda, False)
+    eng = OnlineF2F(net)
+    eng.finetune(fr[1], fr[0], fl[1], 3)
+    fn = str(tmp_path / "final.pth")
+    torch.save([eng.model, eng.optimizer], fn)
+    model2, opt2 = torch.load(fn, weights_only=False)
+    eng2 = OnlineF2F(model2, optimizer=opt2)
+    assert torch.equal(eng2.net.flat_params, eng.net.flat_params) and torch.equal(eng2.net._running, eng.net._running)
+    la, lb = [], []
+    eng.finetune(fr[2], fr[1], fl[2], 3, la)
+    eng2.finetune(fr[2], fr[1], fl[2], 3, lb)
+    assert eng2.optimizer._flat_state[0]["step"] == eng.optimizer._flat_state[0]["step"] == 6
+    assert np.allclose(la, lb, rtol=1e-6)
+    assert _rel(eng2.net.flat_params, eng.net.flat_params) <= 1e-6
+    m3 = load_network(fn, cuda)                 # a saved [model, optimizer] file as --network
+    assert _rel(m3.module.flat_params, model2.module.flat_params) <= 1e-3   # model2 trained 3 more iterations since the save
+
+
 def test_config0_sequence_against_golden_oracle(cuda):
     """BASELINE.json configs[0] (the reference's own CPU-runnable case): 10-frame 960x540 gray sigma = 25 synthetic
     sequence with its analytic flows, DnCNN-25 layout, iter = 20.  The FP32 CPU oracle loop's per-frame PSNRs and

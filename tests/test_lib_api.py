@@ -43,3 +43,16 @@ def test_load_model_checkpoint_and_forward_convention(cuda, tmp_path):
     flow = torch.from_numpy(synth.backward_flow(H, W, 1))[None]
     loss = crit(y[0, 1:2], x[0, 0:1].to(cuda), flow, 0)
     assert loss.ndim == 0 and float(loss) > 0
+
+
+def test_reference_package_name_is_importable():
+    """`import frame2frame` -- what an unmodified harness does (setup.py:18-32, lib/frame2frame/__init__.py:1-39)."""
+    import frame2frame
+    from frame2frame_b200 import lib_api
+    assert frame2frame.WarpedLoss is lib_api.WarpedLoss and frame2frame.load_model is lib_api.load_model
+    assert frame2frame.extract_model_config({"channels": 1})["channels"] == 1
+    assert frame2frame.dncnn.load_model is lib_api.load_model and frame2frame.dncnn.DnCNN.__name__ == "DnCNN"
+    with pytest.raises(ImportError):
+        frame2frame.lightning                                       # out of scope, says why
+    with pytest.raises(AttributeError):
+        frame2frame.nonsense

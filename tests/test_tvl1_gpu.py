@@ -129,6 +129,43 @@ def test_1080p_properties(cuda):
     print("1080p iters (scale x warp):", iters[0].tolist())
 
 
+def test_1080p_pair_equals_oracle(cuda):
+    """One pair at the metric's frame size against the CPU oracle inside the suite (about 2-6 s of host time):
+    identical per-(scale, warp) iteration counts, flow within the 1e-3 px bar (in practice bit-equal)."""
+    H, W = 1080, 1920
+    I0, I1 = synth.noisy_frame(H, W, 1), synth.noisy_frame(H, W, 0)
+    flow, iters = tvl1flow(dev(I0, cuda), dev(I1, cuda), return_iters=True, nscales=5)
+    u, it, _ = OracleTvl1().flow(I0, I1, nscales=5)
+    assert np.array_equal(iters, it), (iters.tolist(), it.tolist())
+    d = float(np.abs(flow.cpu().numpy() - u).max())
+    assert d <= FLOW_TOL, d
+    print("1080p pair: max|flow - oracle| = %g px, %d inner iterations at the finest scale" % (d, int(it[0].sum())))
+
+
+def test_reference_symbol_drop_in(cuda):
+    """The exported drop-in `Dual_TVL1_optic_flow_multiscale` (tvl1flow_lib.c:356-372: same name, same 15 arguments,
+    host buffers, caller-allocated u1/u2, no return value) called the way main.c:176-181 calls the reference's, against
+    the reference's own library when it is built (oracle/_ref) and the C restatement otherwise."""
+    import ctypes as C
+    from oracle.tvl1 import RefTvl1, clamp_scales
+    lib = _lib.lib()
+    H, W = 120, 200
+    I0, I1 = synth.noisy_frame(H, W, 1), synth.noisy_frame(H, W, 0)
+    fp = C.POINTER(C.c_float)
+    for kw in (dict(lam=0.15, nscales=100, fscale=0), dict(lam=0.2, nscales=100, fscale=2)):
+        ns, fs = clamp_scales(W, H, 0.5, kw["nscales"], kw["fscale"])          # main.c:159-163 runs before the call
+        a0, a1 = I0.copy(), I1.copy()
+        u = np.full((2, H, W), np.nan, np.float32)
+        lib.Dual_TVL1_optic_flow_multiscale.restype = None
+        lib.Dual_TVL1_optic_flow_multiscale(a0.ctypes.data_as(fp), a1.ctypes.data_as(fp), u[0].ctypes.data_as(fp),
+                                            u[1].ctypes.data_as(fp), C.c_int(W), C.c_int(H), C.c_float(0.25),
+                                            C.c_float(kw["lam"]), C.c_float(0.3), C.c_int(ns), C.c_int(fs), C.c_float(0.5),
+                                            C.c_int(5), C.c_float(0.01), C.c_bool(False))
+        assert np.array_equal(a0, I0) and np.array_equal(a1, I1)                # inputs are not modified
+        ref = RefTvl1().flow(I0, I1, **kw) if RefTvl1.available() else OracleTvl1().flow(I0, I1, **kw)[0]
+        assert np.abs(u - ref).max() <= FLOW_TOL, kw
+
+
 def test_inline_division_is_ieee(cuda):
     # the iteration kernel divides with a refined reciprocal + two residual corrections;
     # it must agree bit-for-bit with IEEE division on the operand ranges of the solver

@@ -15,8 +15,8 @@ fine-tuning iterations had to repair the network and the eval output lost 2-6 dB
 operating point of a real pretrained DnCNN, whose patch batches, dataset and single images share their
 statistics.  This generator therefore (1) trains on images of one family (the synthetic sequence
 generator at random phases plus contrast-matched sinusoid/edge mixtures), (2) ends with a phase whose
-batches come from ONE image each, the regime the F2F loop runs in, and (3) re-estimates the running
-statistics as the plain average of per-image batch statistics.  The script prints train- vs
+batches are ONE whole image each (N = 1, full frame), the regime the F2F loop runs in, and (3) re-estimates
+the running statistics as the plain average of per-image batch statistics over the generator's frames.  The script prints train- vs
 eval-mode PSNR and a 3-frame F2F fine-tuning trajectory so that the consistency is on record.
 """
 import os
@@ -84,33 +84,62 @@ for it in range(n1):                                   # phase 1: mixed patch ba
     if it % 500 == 0 or it == n1 - 1:
         print("phase 1 iter %d loss %.4f" % (it, float(loss)), flush=True)
 
-# phase 2: every batch comes from ONE image (4 crops of 160x160): per-image batch statistics, the F2F regime
+# phase 2: every batch is ONE image (N = 1): per-image batch statistics, the regime the F2F loop runs in.  The image is a
+# whole 640x360 training frame, a whole 960x540 frame of the generator, or a 640x360 window of one of its 1920x1080
+# frames, so that the statistics of small frames, large frames and parts of large frames are all seen.
 n2 = iters - n1
+NGEN = 40                                              # images 0..39 are frames of the synthetic generator
+mk = lambda h, w, ts: torch.from_numpy(np.stack([synth.clean_frame_u8(h, w, t) for t in ts])).to(dev)
+clean540, clean1080 = mk(540, 960, range(1, 120, 8)), mk(1080, 1920, range(2, 120, 10))
 opt = torch.optim.Adam(net.parameters(), lr=2e-4)
 sched = torch.optim.lr_scheduler.MultiStepLR(opt, [int(n2 * 0.5), int(n2 * 0.8)], 0.25)
-B2, PS2 = 4, 160
 for it in range(n2):
-    i = int(torch.randint(0, NI, (1,)))
-    ys = torch.randint(0, H - PS2, (B2,)).tolist()
-    xs = torch.randint(0, W - PS2, (B2,)).tolist()
-    patch = torch.stack([clean[i, y:y + PS2, x:x + PS2] for y, x in zip(ys, xs)])[:, None]
-    noisy, cl = corrupt(patch)
-    loss = ((net(noisy) - (noisy - cl)) ** 2).sum() / (2 * B2)
+    r = it % 8
+    if r in (3, 7):
+        img = clean[int(torch.randint(0, NI, (1,)))]
+    elif r in (1, 5):
+        img = clean540[int(torch.randint(0, clean540.shape[0], (1,)))]
+    elif r in (2, 6):
+        big = clean1080[int(torch.randint(0, clean1080.shape[0], (1,)))]
+        y, x = int(torch.randint(0, 1080 - H, (1,))), int(torch.randint(0, 1920 - W, (1,)))
+        img = big[y:y + H, x:x + W]
+    else:
+        img = clean[int(torch.randint(0, NGEN, (1,)))]
+    img = img[None, None]
+    if (it // 8) % 2:
+        img = img.flip(-1)
+    noisy, cl = corrupt(img)
+    loss = ((net(noisy) - (noisy - cl)) ** 2).sum() / 2 * (2500.0 / img.numel())     # per 50x50 px like phase 1
     opt.zero_grad()
     loss.backward()
     opt.step()
     sched.step()
     if it % 500 == 0 or it == n2 - 1:
         print("phase 2 iter %d loss %.4f" % (it, float(loss)), flush=True)
+# phase 3: a few whole 1920x1080 frames (the metric's size) at the final learning rate
+for it in range(int(n2 * 0.05)):
+    noisy, cl = corrupt(clean1080[it % clean1080.shape[0]][None, None])
+    loss = ((net(noisy) - (noisy - cl)) ** 2).sum() / 2 * (2500.0 / noisy.numel())
+    opt.zero_grad()
+    loss.backward()
+    opt.step()
+print("phase 3 last loss %.4f" % float(loss), flush=True)
 
-# running statistics = plain average of per-image batch statistics (momentum=None: cumulative average)
+# running statistics = plain average of per-image batch statistics over the generator's frames at the three sizes
+# (momentum=None: cumulative average) -- the pretrained network is "in distribution" for the sequences it will denoise,
+# as DnCNN-S-25 is for natural video
 for m in net.modules():
     if isinstance(m, torch.nn.BatchNorm2d):
         m.reset_running_stats()
         m.momentum = None
 with torch.no_grad():
-    for i in range(NI):
+    for i in range(NGEN):
         net(corrupt(clean[i][None, None])[0])
+    for i in range(clean540.shape[0]):
+        net(corrupt(clean540[i][None, None])[0])
+    for rep in range(2):
+        for i in range(clean1080.shape[0]):
+            net(corrupt(clean1080[i][None, None])[0])
 for m in net.modules():
     if isinstance(m, torch.nn.BatchNorm2d):
         m.momentum = 0.1
@@ -122,7 +151,7 @@ print("saved", out, os.path.getsize(out))
 
 # ---- on record: train- vs eval-mode forward, and the F2F fine-tuning trajectory (stock PyTorch FP32) ----
 ps = lambda a, b: float(10 * torch.log10(1.0 / ((a - b) ** 2).mean()))
-for Hh, Ww in ((216, 384), (540, 960)):
+for Hh, Ww in ((216, 384), (540, 960), (1080, 1920)):
     c = torch.from_numpy(synth.clean_frame_u8(Hh, Ww, 3) / 255.0).float().to(dev)[None, None]
     n = torch.from_numpy(synth.noisy_frame(Hh, Ww, 3) / 255.0).float().to(dev)[None, None]
     with torch.no_grad():
