@@ -31,6 +31,7 @@ def _declare(lib):
     lib.f2f_tvl1_workspace_bytes.argtypes = [C.c_int, C.c_int, C.POINTER(Tvl1Params), C.c_int]
     lib.f2f_tvl1_workspace_bytes.restype = sz
     lib.f2f_tvl1_flow_batch.argtypes = [fp, fp, fp, C.c_int, C.c_int, C.c_int, C.POINTER(Tvl1Params), ip, vp, sz, vp]
+    lib.f2f_tvl1_flow_bidir.argtypes = [fp, fp, fp, C.c_int, C.c_int, C.c_int, C.POINTER(Tvl1Params), ip, vp, sz, vp]
     lib.f2f_tvl1_flow_batch_host.argtypes = [fp, fp, fp, C.c_int, C.c_int, C.c_int, C.POINTER(Tvl1Params), ip, C.c_int]
     lib.f2f_tvl1_gaussian.argtypes = [fp, C.c_int, C.c_int, C.c_double, fp, vp]
     lib.f2f_tvl1_zoom_out.argtypes = [fp, fp, C.c_int, C.c_int, C.c_float, fp, vp]
@@ -59,6 +60,9 @@ def _declare(lib):
     lib.f2f_set_conv_pair.argtypes = [C.c_int]
     lib.f2f_set_conv_pair.restype = None
     lib.f2f_dncnn_storage_dtype.restype = C.c_int
+    lib.f2f_dncnn_set_precise.argtypes = [C.c_int]
+    lib.f2f_dncnn_set_precise.restype = None
+    lib.f2f_dncnn_get_precise.restype = C.c_int
     lib.f2f_dncnn_forward.argtypes = [fp, fp, vp, fp, fp, vp, sz, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp]
     lib.f2f_dncnn_backward.argtypes = [fp, fp, fp, vp, sz, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp]
     lib.f2f_adam_step.argtypes = [fp, fp, fp, fp, sz, C.c_longlong, C.c_float, C.c_float, C.c_float, C.c_float,

@@ -144,8 +144,8 @@ class BatchF2F:
         self._shape = None
 
     def _buffers(self, H, W):
-        if self._shape != (H, W):
-            from ._lib import lib
+        from ._lib import lib
+        if self._shape != (H, W, lib().f2f_dncnn_get_precise()):
             n = len(self.local)
             mk = lambda *s, dt=torch.float32: torch.empty(s, dtype=dt, device=self.dev)
             self._out, self._dout = mk(1, 1, H, W), mk(1, 1, H, W)
@@ -156,7 +156,7 @@ class BatchF2F:
             lay = (C.c_size_t * 8)()
             lib().f2f_dncnn_workspace_layout(1, H, W, 1, lay)
             self._stats_off = int(lay[7])
-            self._shape = (H, W)
+            self._shape = (H, W, lib().f2f_dncnn_get_precise())
 
     def finetune(self, currs, prevs, flows, iters=20, losses=None):
         """One frame of every LOCAL sequence: currs/prevs [1,1,H,W] lists, flows [1,2,H,W] list (frame
@@ -166,7 +166,7 @@ class BatchF2F:
         if not (len(currs) == len(prevs) == len(flows) == len(self.local)):
             raise ValueError("expected %d local sequences" % len(self.local))
         currs = [c.to(self.dev, torch.float32).contiguous() for c in currs]
-        H, W = (currs[0].shape[-2:] if currs else self._shape)
+        H, W = (currs[0].shape[-2:] if currs else self._shape[:2])
         self._buffers(H, W)
         self.model.train()
         pre = [self.criterion.precompute(p, f) for p, f in zip(prevs, flows)]          # once per frame

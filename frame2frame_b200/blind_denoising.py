@@ -194,6 +194,9 @@ def blind_denoising(**args):
     # everything below (pinned-buffer copies, the `ready` events, the prefetch workers' pin_memory) acts on the CURRENT
     # device and its current stream: make that this run's GPU, not cuda:0 (--gpu N, torchrun ranks with LOCAL_RANK >= 1)
     torch.cuda.set_device(dev)
+    if args.get("precise"):
+        from .dncnn import set_precise
+        set_precise(True)
     model_fn = args["network"]
     if not os.path.isabs(model_fn):
         model_fn = os.path.join(os.path.abspath(os.path.dirname(__file__)), model_fn)
@@ -306,6 +309,9 @@ def main(argv=None):
     parser.add_argument("--network", type=str, default="dncnn/logs/DnCNN-S-25/net.pth", help="path to the network")
     parser.add_argument("--gpu", type=int, default=0, help="(added) CUDA device index")
     parser.add_argument("--align_corners", action="store_true", help="(added) sample with align_corners=True")
+    parser.add_argument("--precise", action="store_true",
+                        help="(added) FP32 arithmetic throughout the network (the reference's precision; ~25x slower than the "
+                             "default 16-bit tensor-core operands)")
     parser.add_argument("--lookahead", type=int, default=16, help="(added) frame pairs per batched TV-L1 call when --flow is empty")
     # (added) TV-L1 parameters of the on-device flow used when --flow is empty; defaults = tvl1flow/tvl1flow.sh:11-18
     for name, typ in (("tau", float), ("lam", float), ("theta", float), ("nscales", int), ("fscale", int), ("zfactor", float),

@@ -771,6 +771,11 @@ static int simt_blocks() { return num_sms() * 4; }
 
 static void *g_debug_dump = nullptr;   // see f2f_dncnn_set_debug_dump
 
+// 0: the default mode (16-bit tensor-core operands), 1: the FP32 mode of dncnn_precise.cuh (f2f_dncnn_set_precise)
+static int g_precise = getenv("F2F_PRECISE") ? atoi(getenv("F2F_PRECISE")) : 0;
+
+#include "dncnn_precise.cuh"
+
 }  // namespace net
 }  // namespace f2f
 
@@ -781,9 +786,13 @@ extern "C" {
 
 size_t f2f_dncnn_param_count(void) { return NPARAMS; }
 
+void f2f_dncnn_set_precise(int on) { g_precise = on != 0; }
+int f2f_dncnn_get_precise(void) { return g_precise; }
+
 size_t f2f_dncnn_workspace_bytes(int B, int H, int W, int train)
 {
     if (B < 1 || H < 1 || W < 1) return 0;
+    if (g_precise) return pr::make_plan_f(B, H, W, train).total;
     return make_plan(B, H, W, train).total;
 }
 
@@ -791,6 +800,12 @@ void f2f_dncnn_set_debug_dump(void *d_buf) { g_debug_dump = d_buf; }
 
 void f2f_dncnn_workspace_layout(int B, int H, int W, int train, size_t out[8])
 {
+    if (g_precise) {
+        const pr::PlanF p = pr::make_plan_f(B, H, W, train);
+        out[0] = p.o_x; out[1] = p.o_a0; out[2] = p.o_z; out[3] = p.act_bytes; out[4] = p.o_g0; out[5] = p.o_g1;
+        out[6] = p.o_coef; out[7] = p.o_stats_f;
+        return;
+    }
     const Plan p = make_plan(B, H, W, train);
     out[0] = p.o_x; out[1] = p.o_a0; out[2] = p.o_z; out[3] = p.act_bytes; out[4] = p.o_g0; out[5] = p.o_g1;
     out[6] = p.o_coef; out[7] = p.o_stats_f;
@@ -803,6 +818,8 @@ int f2f_dncnn_forward(const float *d_params, float *d_bn_running, long long *d_n
         set_error("f2f_dncnn_forward: bad arguments");
         return F2F_EINVAL;
     }
+    if (g_precise)
+        return pr::forward(d_params, d_bn_running, d_nbt, d_x, d_y, d_ws, ws_bytes, B, H, W, train, residual, (cudaStream_t)stream);
     const Plan pl = make_plan(B, H, W, train);
     if (ws_bytes < pl.total) {
         set_error("f2f_dncnn_forward: workspace too small (%zu bytes, need %zu)", ws_bytes, pl.total);
@@ -904,6 +921,8 @@ int f2f_dncnn_backward(const float *d_params, float *d_grads, const float *d_dy,
         set_error("f2f_dncnn_backward: bad arguments");
         return F2F_EINVAL;
     }
+    if (g_precise)
+        return pr::backward(d_params, d_grads, d_dy, d_ws, ws_bytes, B, H, W, residual, accumulate, (cudaStream_t)stream);
     const Plan pl = make_plan(B, H, W, 1);
     if (ws_bytes < pl.total) {
         set_error("f2f_dncnn_backward: workspace too small (%zu bytes, need %zu)", ws_bytes, pl.total);

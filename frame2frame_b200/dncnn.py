@@ -30,6 +30,17 @@ def _stream():
     return torch.cuda.current_stream().cuda_stream
 
 
+def set_precise(on):
+    """Precision mode of every DnCNN in the process (f2f_dncnn_set_precise): False = the default 16-bit tensor-core
+    operands, True = the FP32 CUDA-core mode, the arithmetic of the reference's FP32 torch loop up to summation order
+    (about 25x slower).  Workspaces are re-planned on the next call."""
+    lib().f2f_dncnn_set_precise(int(bool(on)))
+
+
+def get_precise():
+    return bool(lib().f2f_dncnn_get_precise())
+
+
 class _Workspace:
     """Device workspace of f2f_dncnn_forward/backward, cached per (B, H, W, train, device)."""
 
@@ -38,7 +49,7 @@ class _Workspace:
         self.buf = None
 
     def get(self, B, H, W, train, device):
-        key = (B, H, W, bool(train), str(device))
+        key = (B, H, W, bool(train), str(device), lib().f2f_dncnn_get_precise())
         if self.key != key:
             n = lib().f2f_dncnn_workspace_bytes(B, H, W, int(train))
             if n == 0:

@@ -72,6 +72,41 @@ def tvl1flow(I0, I1, nslots=16, return_iters=False, **kw):
     return (flow, iters) if return_iters else flow
 
 
+def tvl1flow_bidir(A, B, nslots=16, return_iters=False, **kw):
+    """Forward AND backward flow of every pair (A[k], B[k]) in one pass with shared pyramids (tvl1flow.sh:11-18 computes
+    them as two processes per frame): -> (flow A->B [N,2,H,W], flow B->A [N,2,H,W]), bit-identical to
+    tvl1flow(A, B), tvl1flow(B, A).  A, B: float32 CUDA tensors [N,H,W] or [H,W]."""
+    if not A.is_cuda:
+        raise RuntimeError("tvl1flow_bidir needs CUDA tensors: there is no CPU fallback in this package")
+    squeeze = A.dim() == 2
+    if squeeze:
+        A, B = A[None], B[None]
+    A, B = A.contiguous().float(), B.contiguous().float()
+    if A.shape != B.shape or A.dim() != 3:
+        raise ValueError("input images size mismatch %s != %s" % (tuple(A.shape), tuple(B.shape)))
+    n, ny, nx = A.shape
+    p = make_params(nx, ny, **kw)
+    nslots = max(2, min(nslots, 2 * n) & ~1)
+    key = (nx, ny, p.nscales, p.nwarps, nslots, str(A.device))
+    ws = _ws_cache.get(key)
+    if ws is None:
+        _ws_cache.clear()
+        ws = _ws_cache[key] = Tvl1Workspace(nx, ny, p, nslots, A.device)
+    flow = torch.empty((n, 2, 2, ny, nx), dtype=torch.float32, device=A.device)
+    iters = np.zeros((n, 2, p.nscales, p.nwarps), np.int32) if return_iters else None
+    if n:
+        with torch.cuda.device(A.device):
+            st = torch.cuda.current_stream().cuda_stream
+            check(lib().f2f_tvl1_flow_bidir(A.data_ptr(), B.data_ptr(), flow.data_ptr(), n, nx, ny, C.byref(p),
+                                            iters.ctypes.data if iters is not None else None,
+                                            ws.buf.data_ptr(), ws.nbytes, st), "f2f_tvl1_flow_bidir")
+    fwd, bwd = flow[:, 0], flow[:, 1]
+    if squeeze:
+        fwd, bwd = fwd[0], bwd[0]
+        iters = iters[0] if iters is not None else None
+    return (fwd, bwd, iters) if return_iters else (fwd, bwd)
+
+
 def tvl1flow_host(I0, I1, max_slots=16, return_iters=False, **kw):
     """Same through host (numpy) buffers: H2D, batch, D2H inside the library."""
     I0 = np.ascontiguousarray(I0, np.float32)

@@ -16,7 +16,7 @@ import sys
 import numpy as np
 import torch
 
-from .tvl1 import tvl1flow, write_flo
+from .tvl1 import tvl1flow, tvl1flow_bidir, write_flo
 
 DEFAULTS = [("out", str, "flow.flo"), ("nproc", int, 4), ("tau", float, 0.25), ("lam", float, 0.15),
             ("theta", float, 0.3), ("nscales", int, 100), ("fscale", int, 0), ("zfactor", float, 0.5),
@@ -74,10 +74,28 @@ def main(argv=None, device=None):
         if not jobs:
             return 0
         frames = {i: read_gray(pattern % i) for i in sorted({a for a, _, _ in jobs} | {b for _, b, _ in jobs})}
-        I0, I1, names = [frames[a] for a, _, _ in jobs], [frames[b] for _, b, _ in jobs], [n for _, _, n in jobs]
-        flow = tvl1flow(torch.from_numpy(np.stack(I0)).to(dev), torch.from_numpy(np.stack(I1)).to(dev), **SCRIPT_PARAMS)
-        for f, name in zip(flow, names):
-            write_flo(name, f)
+        # the script's two flows of a frame pair (bflow then fflow, adjacent in the job list) share their pyramids
+        k = 0
+        pairs, singles = [], []
+        while k < len(jobs):
+            if k + 1 < len(jobs) and jobs[k][0] == jobs[k + 1][1] and jobs[k][1] == jobs[k + 1][0]:
+                pairs.append((jobs[k], jobs[k + 1]))
+                k += 2
+            else:
+                singles.append(jobs[k])
+                k += 1
+        if pairs:
+            A = torch.from_numpy(np.stack([frames[j0[0]] for j0, _ in pairs])).to(dev)
+            B = torch.from_numpy(np.stack([frames[j0[1]] for j0, _ in pairs])).to(dev)
+            fab, fba = tvl1flow_bidir(A, B, **SCRIPT_PARAMS)
+            for (j0, j1), f0, f1 in zip(pairs, fab, fba):
+                write_flo(j0[2], f0)
+                write_flo(j1[2], f1)
+        if singles:                                        # a rank's block may start or end in the middle of a pair
+            flow = tvl1flow(torch.from_numpy(np.stack([frames[a] for a, _, _ in singles])).to(dev),
+                            torch.from_numpy(np.stack([frames[b] for _, b, _ in singles])).to(dev), **SCRIPT_PARAMS)
+            for f, (_, _, name) in zip(flow, singles):
+                write_flo(name, f)
         return 0
     v = parse_positionals(argv)
     I0, I1 = read_gray(v["I0"]), read_gray(v["I1"])

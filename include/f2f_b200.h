@@ -94,6 +94,17 @@ int f2f_tvl1_flow_batch(const float *d_I0, const float *d_I1, float *d_u,
                         int32_t *h_iters, void *d_workspace, size_t ws_bytes,
                         void *stream);
 
+/* Both directions of every pair in one pass -- what tvl1flow.sh:11-18 runs as two processes per frame (fflow: I0 = frame
+ * i, I1 = frame i+1; bflow: the reverse).  The joint normalisation, the pre-smoothing and the two pyramids
+ * (tvl1flow_lib.c:393-414) do not depend on the direction and are built once per pair.
+ *   d_A, d_B : [npairs][ny][nx]
+ *   d_u      : [npairs][2][2][ny][nx]: direction 0 = flow from A to B (I0 = A, I1 = B), direction 1 = from B to A
+ *   h_iters  : optional [npairs][2][nscales][nwarps]
+ * Results are bit-identical to two f2f_tvl1_flow_batch calls. */
+int f2f_tvl1_flow_bidir(const float *d_A, const float *d_B, float *d_u, int npairs, int nx, int ny,
+                        const f2f_tvl1_params *p, int32_t *h_iters, void *d_workspace, size_t ws_bytes,
+                        void *stream);
+
 /* Same, for HOST buffers: uploads the frames, runs the batch and downloads the
  * flows (device memory is allocated inside and cached between calls; release
  * with f2f_release()).  This is the call a host program that used to run one
@@ -193,7 +204,7 @@ int f2f_dncnn_dgrad64(const void *d_dz, void *d_gout, const void *d_wprep_t, con
  *              applied on load) or a post-ReLU activation (d_coef_in = NULL)
  *   d_g, d_z : masked output gradient (in) / dz (out), and the layer's pre-BN output
  *   d_coef   : the layer's own coefficient block (A, B, C used)
- *   d_partial: scratch, 148 * 49152 floats; d_dw: [64][64][3][3] FP32 (PyTorch layout). */
+ *   d_partial: scratch, (number of SMs) * 49152 floats; d_dw: [64][64][3][3] FP32 (PyTorch layout). */
 int f2f_dncnn_wgrad64(const void *d_act, const float *d_coef_in, void *d_g, const void *d_z,
                       const float *d_coef, float *d_partial, float *d_dw, int H, int W,
                       int accumulate, void *stream);
@@ -227,8 +238,15 @@ void f2f_dncnn_set_debug_dump(void *d_buf);
  * issuer waiting for a drained accumulator / a staged tile / issuing; [5],[6] epilogue waiting for
  * accumulators / draining a tile; [7] epilogue loop total; [8] tiles.  NULL switches it off. */
 void f2f_dncnn_set_trace(unsigned long long *d_counters);
-/* Development aid: on != 0 routes the BN+ReLU-prologue convolutions to the older register-staged
- * kernel (dn::k_conv64) instead of the TMA-fed one with in-place transform warps, for comparison. */
+/* Precision mode of the whole-network entry points (f2f_dncnn_forward / _backward / f2f_step_train and
+ * f2f_dncnn_workspace_bytes / _layout, which must be asked again after a switch):
+ *   0 (default): activations, gradients and tensor-core operands in 16 bits, FP32 accumulation (tcgen05);
+ *   1 ("precise"): everything in FP32 on the CUDA cores (csrc/dncnn_precise.cuh) -- the arithmetic of the reference's
+ *      FP32 torch path (blind_denoising.py:211-230) up to summation order, ~25x slower; the setting in which the
+ *      online loop is held to north_star's 0.05 dB PSNR tolerance independently of 16-bit rounding.
+ * F2F_PRECISE in the environment sets the initial value.  Process-global, like the other switches. */
+void f2f_dncnn_set_precise(int on);
+int f2f_dncnn_get_precise(void);
 /* Programmatic dependent launch of the per-layer DnCNN kernel chain: bit mask, default 3 (launch attribute on the big
  * and the small kernels, no early trigger); 0 launches the same kernels fully serialised (F2F_PDL in the environment
  * sets the initial value).  Results are identical, only the gaps between kernels differ (csrc/f2f_common.cuh). */

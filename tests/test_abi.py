@@ -100,19 +100,23 @@ def test_tvl1flow_cli_sequence_follows_the_script(tmp_path, monkeypatch):
         np.save(tmp_path / ("f%03d.npy" % i), np.full((6, 8), float(i), np.float32))
     calls, written = [], {}
 
-    def fake_flow(I0, I1, **kw):
-        calls.append((I0[:, 0, 0].tolist(), I1[:, 0, 0].tolist(), kw))
-        return torch.stack([torch.full((2, 6, 8), float(k)) for k in range(I0.shape[0])])
+    def fake_bidir(A, B, **kw):
+        # both directions of every pair in one pass (shared pyramids): flow A -> B tagged 10k, B -> A tagged 10k + 1
+        calls.append((A[:, 0, 0].tolist(), B[:, 0, 0].tolist(), kw))
+        n = A.shape[0]
+        return (torch.stack([torch.full((2, 6, 8), 10.0 * k) for k in range(n)]),
+                torch.stack([torch.full((2, 6, 8), 10.0 * k + 1) for k in range(n)]))
 
-    monkeypatch.setattr(cli, "tvl1flow", fake_flow)
+    monkeypatch.setattr(cli, "tvl1flow_bidir", fake_bidir)
+    monkeypatch.setattr(cli, "tvl1flow", lambda *a, **k: (_ for _ in ()).throw(AssertionError("whole pairs go through bidir")))
     monkeypatch.setattr(cli, "write_flo", lambda name, f: written.__setitem__(name, float(f[0, 0, 0])))
     out = str(tmp_path / "o%03d")
     assert cli.main(["--sequence", str(tmp_path / "f%03d.npy"), "1", "2", out], device="cpu") == 0
-    (i0, i1, kw), = calls
-    assert i0 == [2.0, 1.0, 3.0, 2.0] and i1 == [1.0, 2.0, 2.0, 3.0]         # bflow(1), fflow(1), bflow(2), fflow(2)
+    (a, b, kw), = calls
+    assert a == [2.0, 3.0] and b == [1.0, 2.0]          # pair i: A = frame i+1, B = frame i; A -> B is the bflow, B -> A the fflow
     assert kw == dict(tau=0.25, lam=0.2, theta=0.3, nscales=100, fscale=2, zfactor=0.5, nwarps=5, epsilon=0.01)
-    assert written == {out % 2 + "_bflow.flo": 0.0, out % 1 + "_fflow.flo": 1.0, out % 3 + "_bflow.flo": 2.0,
-                       out % 2 + "_fflow.flo": 3.0}
+    assert written == {out % 2 + "_bflow.flo": 0.0, out % 1 + "_fflow.flo": 1.0, out % 3 + "_bflow.flo": 10.0,
+                       out % 2 + "_fflow.flo": 11.0}
 
 
 def test_missing_library_fails_loudly_no_cpu_fallback():
@@ -150,8 +154,17 @@ def test_tvl1flow_cli_sequence_shards_pairs_over_ranks(tmp_path, monkeypatch):
         np.save(tmp_path / ("f%03d.npy" % i), np.full((4, 4), float(i), np.float32))
     written = []
     monkeypatch.setattr(cli, "tvl1flow", lambda I0, I1, **kw: torch.zeros(I0.shape[0], 2, 4, 4))
+    monkeypatch.setattr(cli, "tvl1flow_bidir", lambda A, B, **kw: (torch.zeros(A.shape[0], 2, 4, 4), torch.zeros(A.shape[0], 2, 4, 4)))
     monkeypatch.setattr(cli, "write_flo", lambda name, f: written.append(os.path.basename(name)))
     for rank in range(3):
         monkeypatch.setenv("RANK", str(rank)); monkeypatch.setenv("WORLD_SIZE", "3")
         assert cli.main(["--sequence", str(tmp_path / "f%03d.npy"), "1", "3", str(tmp_path / "o%03d")], device="cpu") == 0
-    assert written == ["o002_bflow.flo", "o001_fflow.flo", "o003_bflow.flo", "o002_fflow.flo", "o004_bflow.flo", "o003_fflow.flo"]
+    # every file exactly once; within a rank whole pairs (shared pyramids) are written before a block's odd field
+    assert sorted(written) == sorted(["o002_bflow.flo", "o001_fflow.flo", "o003_bflow.flo", "o002_fflow.flo", "o004_bflow.flo",
+                                      "o003_fflow.flo"])
+    # a 4-rank split of 5 frames cuts pairs in the middle: the halves still come out, through the single-direction path
+    written.clear()
+    for rank in range(4):
+        monkeypatch.setenv("RANK", str(rank)); monkeypatch.setenv("WORLD_SIZE", "4")
+        assert cli.main(["--sequence", str(tmp_path / "f%03d.npy"), "1", "3", str(tmp_path / "o%03d")], device="cpu") == 0
+    assert len(written) == 6 and len(set(written)) == 6

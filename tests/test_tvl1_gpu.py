@@ -203,3 +203,21 @@ def test_tvl1flow_command_lines(cuda, tmp_path):
     # size mismatch -> error return like main.c:189-193
     Image.fromarray(fr[0][:40].astype(np.uint8)).save(str(tmp_path / "small.png"))
     assert tvl1flow_cli.main([str(tmp_path / "small.png"), str(tmp_path / "f_000.png"), out]) == 1
+
+
+def test_both_directions_share_their_pyramids(cuda):
+    """the forward and backward flow of a frame pair (tvl1flow.sh:11-18 runs two processes) in ONE pass with
+    one set of pyramids (f2f_tvl1_flow_bidir) must equal the two separate batches bit for bit, iteration counts
+    included -- an odd number of pairs, fewer slots than fields, the script's parameters (lambda 0.2, fscale 2)."""
+    from frame2frame_b200.tvl1 import tvl1flow_bidir
+    H, W, n = 90, 160, 3
+    A = dev(np.stack([synth.noisy_frame(H, W, t + 1, seq=t) for t in range(n)]), cuda)
+    B = dev(np.stack([synth.noisy_frame(H, W, t, seq=t) for t in range(n)]), cuda)
+    for kw in (dict(nscales=4), dict(lam=0.2, nscales=100, fscale=2)):
+        fab, fba, it = tvl1flow_bidir(A, B, nslots=4, return_iters=True, **kw)
+        ref_ab, it_ab = tvl1flow(A, B, return_iters=True, **kw)
+        ref_ba, it_ba = tvl1flow(B, A, return_iters=True, **kw)
+        assert torch.equal(fab, ref_ab) and torch.equal(fba, ref_ba)
+        assert np.array_equal(it[:, 0], it_ab) and np.array_equal(it[:, 1], it_ba)
+    f1, f2 = tvl1flow_bidir(A[0], B[0], nscales=3)
+    assert f1.shape == (2, H, W) and torch.equal(f1, tvl1flow(A[0], B[0], nscales=3))

@@ -18,7 +18,7 @@ from oracle import dncnn_oracle as do
 H, W, NF, ITERS = (int(v) for v in sys.argv[1:5])
 out_fn = sys.argv[5]
 firsts = [int(v) for v in sys.argv[6:]] or [0]
-threads = os.cpu_count() or 1
+threads = int(os.environ.get("F2F_THREADS", "0")) or os.cpu_count() or 1
 torch.set_num_threads(threads)
 sd = synth.pretrained_state_dict()
 rec = {"frame": "%dx%d" % (W, H), "iters": ITERS, "threads": threads, "torch": torch.__version__,
