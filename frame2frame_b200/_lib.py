@@ -65,6 +65,12 @@ def _declare(lib):
     lib.f2f_dncnn_get_precise.restype = C.c_int
     lib.f2f_dncnn_forward.argtypes = [fp, fp, vp, fp, fp, vp, sz, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp]
     lib.f2f_dncnn_backward.argtypes = [fp, fp, fp, vp, sz, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp]
+    lib.f2f_dncnn_param_count_c.argtypes = [C.c_int]
+    lib.f2f_dncnn_param_count_c.restype = sz
+    lib.f2f_dncnn_workspace_bytes_c.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]
+    lib.f2f_dncnn_workspace_bytes_c.restype = sz
+    lib.f2f_dncnn_forward_c.argtypes = [fp, fp, vp, fp, fp, vp, sz, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp]
+    lib.f2f_dncnn_backward_c.argtypes = [fp, fp, fp, vp, sz, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp]
     lib.f2f_adam_step.argtypes = [fp, fp, fp, fp, sz, C.c_longlong, C.c_float, C.c_float, C.c_float, C.c_float,
                                   C.c_float, vp]
     lib.f2f_step_train.argtypes = [fp, fp, fp, fp, fp, vp, fp, fp, fp, fp, fp, vp, vp, sz, C.c_int, C.c_int, C.c_int,

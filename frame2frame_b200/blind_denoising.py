@@ -64,6 +64,9 @@ class OnlineF2F:
     def __init__(self, model, optimizer=None, align_corners=False):
         self.model = model
         self.net = model.module if isinstance(model, nn.DataParallel) else model
+        if getattr(self.net, "channels", 1) != 1:
+            raise NotImplementedError("the online loop is the paper script's: DnCNN(channels=1) on gray frames "
+                                      "(blind_denoising.py:144)")
         self.dev = self.net.flat_params.device
         self.criterion = WarpedLoss(align_corners=align_corners).cuda(self.dev)
         self.optimizer = optimizer or Adam(model.parameters(), lr=LR, betas=BETAS, eps=EPS, weight_decay=WEIGHT_DECAY,

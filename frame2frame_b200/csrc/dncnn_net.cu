@@ -26,7 +26,6 @@ typedef tc05::h16 h16;
 
 constexpr int NBN = 15;
 constexpr int WSZ = 64 * 64 * 9;                   // 36864
-constexpr size_t OFF_W0 = 0;
 __host__ __device__ constexpr size_t off_conv(int k) { return 576 + (size_t)(k - 1) * (WSZ + 128); }   // k = 1..15
 __host__ __device__ constexpr size_t off_gamma(int k) { return off_conv(k) + WSZ; }
 __host__ __device__ constexpr size_t off_beta(int k) { return off_conv(k) + WSZ + 64; }
@@ -150,13 +149,14 @@ __global__ void k_bn_bwd_coeffs(const double *__restrict__ stats, const float *_
     dbeta[c] = (accumulate ? dbeta[c] : 0.0f) + (float)db * uns;
 }
 
-__global__ void k_small_grads(const double *__restrict__ dw0, const double *__restrict__ dw16, float *__restrict__ grads,
-                              int accumulate, const unsigned *__restrict__ absmax)
+// first / last layer gradients (n = 576 * C values each) from their FP64 accumulators into the gradient vector
+__global__ void k_small_grads(const double *__restrict__ dw0, const double *__restrict__ dw16, float *__restrict__ g_w0,
+                              float *__restrict__ g_w16, int n, int accumulate, const unsigned *__restrict__ absmax)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= 1152) return;
-    float *dst = i < 576 ? grads + OFF_W0 + i : grads + OFF_W16 + (i - 576);
-    const double v = i < 576 ? dw0[i] : dw16[i - 576];
+    if (i >= 2 * n) return;
+    float *dst = i < n ? g_w0 + i : g_w16 + (i - n);
+    const double v = i < n ? dw0[i] : dw16[i - n];
     *dst = (accumulate ? *dst : 0.0f) + (float)v * grad_unscale(absmax);
 }
 
@@ -386,10 +386,26 @@ __global__ void __launch_bounds__(FT) k_first_fwd(const float *__restrict__ x, c
 // haloed 18x18 tile: the lane reads its pixel's 128 bytes (eight 16-byte loads in flight), forms the nine per-tap
 // dot products over all 64 channels with no cross-lane reduction (weights and coefficients are warp-uniform
 // shared-memory reads), and the output pixel sums nine shifted partials from shared memory.
+// Optional fusion of the frame-to-frame loss into the last layer (f2f_step_train): with `warped` set the
+// kernel also forms d = m*out - m*warped, the loss sum / mean, the loss gradient wrt out (what k_masked_loss computes,
+// kinds as f2f_masked_loss) and the bits of max|gradient| for the backward pass's power-of-two scaling (k_absmax) --
+// three launches and one pass over the output fewer per inner iteration.
+struct LossFuse {
+    const float *warped, *mask;
+    float *dout;
+    double *loss;
+    unsigned *absmax;
+    int kind;
+    float inv_n;
+};
+
 __global__ void __launch_bounds__(256) k_last_fwd(const h16 *__restrict__ z, const float *__restrict__ coef,
                                                   const float *__restrict__ w16, const float *__restrict__ x,
-                                                  float *__restrict__ out, int H, int W, int tiles_x, int ntiles, int residual)
+                                                  float *__restrict__ out, int H, int W, int tiles_x, int ntiles, int residual,
+                                                  LossFuse lf)
 {
+    double lacc = 0.0;
+    unsigned amax = 0;
     __shared__ float T[LHP * 9 + 4];
     __shared__ __align__(16) float wS[8 * 72];          // [chunk][tap][8 channels]
     __shared__ __align__(16) float cS[128];             // scale[64], shift[64]
@@ -446,13 +462,294 @@ __global__ void __launch_bounds__(256) k_last_fwd(const h16 *__restrict__ z, con
             for (int t = 0; t < 9; t++) n += T[((y + t / 3) * LH + xx + t % 3) * 9 + t];
             if (gy < H && gx < W) {
                 const size_t i = (size_t)gy * W + gx;
-                out[i] = residual ? x[i] - n : n;
+                const float o = residual ? x[i] - n : n;
+                out[i] = o;
+                if (lf.warped) {                       // blind_denoising.py:121 / warped_loss.py:227,239-248, as k_masked_loss
+                    const float m = lf.mask[i];
+                    const float d = __fsub_rn(__fmul_rn(m, o), __fmul_rn(m, lf.warped[i]));
+                    float g;
+                    if (lf.kind == 0) {
+                        lacc += (double)fabsf(d);
+                        g = m * ((d > 0.0f) ? 1.0f : ((d < 0.0f) ? -1.0f : 0.0f));
+                    } else if (lf.kind == 1) {
+                        lacc += (double)__fmul_rn(d, d);
+                        g = __fmul_rn(m, __fmul_rn(__fmul_rn(2.0f, d), lf.inv_n));
+                    } else {
+                        const float r = sqrtf(__fadd_rn(__fmul_rn(d, d), 1e-6f));
+                        lacc += (double)r;
+                        g = __fmul_rn(m, __fmul_rn(__fdiv_rn(d, r), lf.inv_n));
+                    }
+                    lf.dout[i] = g;
+                    const unsigned b = __float_as_uint(fabsf(g));
+                    amax = b > amax ? b : amax;
+                }
             }
         }
         __syncthreads();
     }
+    if (lf.warped) {
+        __shared__ double sl[8];
+        __shared__ unsigned sa[8];
+        lacc = warp_sum(lacc);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const unsigned v = __shfl_xor_sync(0xffffffffu, amax, o);
+            amax = v > amax ? v : amax;
+        }
+        if ((threadIdx.x & 31) == 0) { sl[threadIdx.x >> 5] = lacc; sa[threadIdx.x >> 5] = amax; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double tsum = 0.0;
+            unsigned m = 0;
+            for (int k = 0; k < 8; k++) { tsum += sl[k]; m = sa[k] > m ? sa[k] : m; }
+            atomicAdd(lf.loss, lf.kind == 0 ? tsum : tsum * (double)lf.inv_n);
+            if (m) atomicMax(lf.absmax, m);
+        }
+    }
 }
 }  // namespace rs
+
+
+// ------------------------------------------------ first / last layer, any channel count and storage type
+// C image channels <-> 64 features (net.py:13-14,19 with `channels` = C; the reference's loader defaults to 3,
+// lib/frame2frame/dncnn/io.py:64-67).  A warp per pixel, a lane owns two feature channels; the image is planar
+// [C][H][W] FP32 like the reference's NCHW tensors, the feature maps NHWC in T = the 16-bit storage type (default mode)
+// or float (precise mode).  The gray-scale default mode keeps its tuned kernels (namespace rs); these serve C != 1 and
+// the precise mode.
+namespace gen {
+template <class T> struct St;
+template <> struct St<h16> {
+    static __device__ __forceinline__ float2 ld(const h16 *p) { return unpack_h16(__ldg(reinterpret_cast<const uint32_t *>(p))); }
+    static __device__ __forceinline__ float2 st(h16 *p, float a, float b)        // -> the values as stored (rounded)
+    {
+        const uint32_t v = pack_h16(a, b);
+        *reinterpret_cast<uint32_t *>(p) = v;
+        return unpack_h16(v);
+    }
+};
+template <> struct St<float> {
+    static __device__ __forceinline__ float2 ld(const float *p) { return __ldg(reinterpret_cast<const float2 *>(p)); }
+    static __device__ __forceinline__ float2 st(float *p, float a, float b)
+    {
+        *reinterpret_cast<float2 *>(p) = make_float2(a, b);
+        return make_float2(a, b);
+    }
+};
+constexpr int NT = 128;                                      // 4 warps per block
+
+template <int NV, class F>
+__device__ __forceinline__ void block_lane_reduce(const float (&v)[NV], float *scratch, F dst)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int i = 0; i < NV; i++) scratch[(warp * NV + i) * 32 + lane] = v[i];
+    __syncthreads();
+    for (int e = threadIdx.x; e < 32 * NV; e += NT) {
+        const int i = e >> 5, l = e & 31;
+        double tsum = 0.0;
+        for (int w = 0; w < NT / 32; w++) tsum += (double)scratch[(w * NV + i) * 32 + l];
+        atomicAdd(dst(l, i), tsum);
+    }
+}
+
+template <int C, class T>
+__global__ void __launch_bounds__(NT) k_first_fwd(const float *__restrict__ x, const float *__restrict__ w0, T *__restrict__ a0,
+                                                  int H, int W)
+{
+    const int lane = threadIdx.x & 31, c0 = 2 * lane;
+    float w[C * 9][2];
+#pragma unroll
+    for (int q = 0; q < C * 9; q++) { w[q][0] = w0[(size_t)c0 * C * 9 + q]; w[q][1] = w0[(size_t)(c0 + 1) * C * 9 + q]; }
+    const size_t P = (size_t)H * W, nw = (size_t)gridDim.x * (NT / 32);
+    for (size_t p = (size_t)blockIdx.x * (NT / 32) + (threadIdx.x >> 5); p < P; p += nw) {
+        const int y = (int)(p / W), xx = (int)(p % W);
+        float s0 = 0.0f, s1 = 0.0f;
+#pragma unroll
+        for (int tp = 0; tp < 9; tp++) {
+            const int yy = y + tp / 3 - 1, xq = xx + tp % 3 - 1;
+            const bool in = yy >= 0 && yy < H && xq >= 0 && xq < W;
+#pragma unroll
+            for (int ci = 0; ci < C; ci++) {
+                const float v = in ? __ldg(x + ci * P + (size_t)yy * W + xq) : 0.0f;
+                s0 = fmaf(v, w[ci * 9 + tp][0], s0); s1 = fmaf(v, w[ci * 9 + tp][1], s1);
+            }
+        }
+        St<T>::st(a0 + p * 64 + c0, fmaxf(s0, 0.0f), fmaxf(s1, 0.0f));
+    }
+}
+
+template <int C, class T>
+__global__ void __launch_bounds__(NT) k_last_fwd(const T *__restrict__ z, const float *__restrict__ coef, const float *__restrict__ w16,
+                                                 const float *__restrict__ x, float *__restrict__ out, int H, int W, int residual)
+{
+    const int lane = threadIdx.x & 31, c0 = 2 * lane;
+    float w[C][9][2];
+#pragma unroll
+    for (int co = 0; co < C; co++)
+#pragma unroll
+        for (int tp = 0; tp < 9; tp++) { w[co][tp][0] = w16[((size_t)co * 64 + c0) * 9 + tp]; w[co][tp][1] = w16[((size_t)co * 64 + c0 + 1) * 9 + tp]; }
+    const float sc0 = coef[C_SCALE + c0], sc1 = coef[C_SCALE + c0 + 1], sh0 = coef[C_SHIFT + c0], sh1 = coef[C_SHIFT + c0 + 1];
+    const size_t P = (size_t)H * W, nw = (size_t)gridDim.x * (NT / 32);
+    for (size_t p = (size_t)blockIdx.x * (NT / 32) + (threadIdx.x >> 5); p < P; p += nw) {
+        const int y = (int)(p / W), xx = (int)(p % W);
+        float s[C];
+#pragma unroll
+        for (int co = 0; co < C; co++) s[co] = 0.0f;
+#pragma unroll
+        for (int tp = 0; tp < 9; tp++) {
+            const int yy = y + tp / 3 - 1, xq = xx + tp % 3 - 1;
+            if (yy >= 0 && yy < H && xq >= 0 && xq < W) {
+                const float2 zz = St<T>::ld(z + ((size_t)yy * W + xq) * 64 + c0);
+                const float a0v = fmaxf(fmaf(zz.x, sc0, sh0), 0.0f), a1v = fmaxf(fmaf(zz.y, sc1, sh1), 0.0f);
+#pragma unroll
+                for (int co = 0; co < C; co++) s[co] = fmaf(a1v, w[co][tp][1], fmaf(a0v, w[co][tp][0], s[co]));
+            }
+        }
+#pragma unroll
+        for (int co = 0; co < C; co++) {
+            const float n = warp_sum(s[co]);
+            if (lane == 0) out[co * P + p] = residual ? x[co * P + p] - n : n;
+        }
+    }
+}
+
+// g15 = relu'(.) * conv^T(dn, w16) (dn = +-scale * dy), its BatchNorm-backward sums, and dW16 -- one pass over z15
+template <int C, class T>
+__global__ void __launch_bounds__(NT) k_last_bwd(const float *__restrict__ dy, float dy_sign, const T *__restrict__ z,
+                                                 const float *__restrict__ coef, const float *__restrict__ w16, T *__restrict__ g,
+                                                 double *__restrict__ stats, double *__restrict__ dw16, int H, int W,
+                                                 const unsigned *__restrict__ absmax)
+{
+    constexpr int NV = C * 18 + 4;
+    __shared__ float scratch[(NT / 32) * NV * 32];
+    dy_sign *= grad_scale(absmax);
+    const int lane = threadIdx.x & 31, c0 = 2 * lane;
+    float w[C][9][2], sc[2], sh[2], is[2], ms[2];
+#pragma unroll
+    for (int j = 0; j < 2; j++) {
+#pragma unroll
+        for (int co = 0; co < C; co++)
+#pragma unroll
+            for (int tp = 0; tp < 9; tp++) w[co][tp][j] = w16[((size_t)co * 64 + c0 + j) * 9 + tp];
+        sc[j] = coef[C_SCALE + c0 + j]; sh[j] = coef[C_SHIFT + c0 + j];
+        is[j] = coef[C_INVSTD + c0 + j]; ms[j] = -coef[C_MEAN + c0 + j] * is[j];
+    }
+    float acc[NV];
+#pragma unroll
+    for (int i = 0; i < NV; i++) acc[i] = 0.0f;
+    const size_t P = (size_t)H * W, nw = (size_t)gridDim.x * (NT / 32);
+    for (size_t p = (size_t)blockIdx.x * (NT / 32) + (threadIdx.x >> 5); p < P; p += nw) {
+        const int y = (int)(p / W), xx = (int)(p % W);
+        const float2 zz = St<T>::ld(z + p * 64 + c0);
+        const float y0 = fmaf(zz.x, sc[0], sh[0]), y1 = fmaf(zz.y, sc[1], sh[1]);
+        const float a0v = fmaxf(y0, 0.0f), a1v = fmaxf(y1, 0.0f);
+        float s0 = 0.0f, s1 = 0.0f;
+#pragma unroll
+        for (int tp = 0; tp < 9; tp++) {
+            // the OUTPUT pixel whose tap tp reads this input pixel: q = p - (tap offset)
+            const int yy = y - (tp / 3 - 1), xq = xx - (tp % 3 - 1);
+            const bool in = yy >= 0 && yy < H && xq >= 0 && xq < W;
+#pragma unroll
+            for (int co = 0; co < C; co++) {
+                const float dn = in ? dy_sign * __ldg(dy + co * P + (size_t)yy * W + xq) : 0.0f;
+                s0 = fmaf(dn, w[co][tp][0], s0); s1 = fmaf(dn, w[co][tp][1], s1);
+                acc[(co * 9 + tp) * 2] = fmaf(a0v, dn, acc[(co * 9 + tp) * 2]);
+                acc[(co * 9 + tp) * 2 + 1] = fmaf(a1v, dn, acc[(co * 9 + tp) * 2 + 1]);
+            }
+        }
+        const float2 gr = St<T>::st(g + p * 64 + c0, y0 > 0.0f ? s0 : 0.0f, y1 > 0.0f ? s1 : 0.0f);   // sums of the STORED gradient
+        acc[C * 18] += gr.x; acc[C * 18 + 1] += gr.y;
+        acc[C * 18 + 2] = fmaf(gr.x, fmaf(zz.x, is[0], ms[0]), acc[C * 18 + 2]);
+        acc[C * 18 + 3] = fmaf(gr.y, fmaf(zz.y, is[1], ms[1]), acc[C * 18 + 3]);
+    }
+    block_lane_reduce<NV>(acc, scratch, [&](int l, int i) -> double * {
+        if (i < C * 18) return dw16 + ((size_t)(i / 18) * 64 + 2 * l + (i & 1)) * 9 + (i % 18) / 2;
+        if (i < C * 18 + 2) return stats + 2 * l + (i - C * 18);
+        return stats + 64 + 2 * l + (i - C * 18 - 2);
+    });
+}
+
+// dW0[oc][ci][tap] = sum_p g0[p][oc] * x[ci][p + tap - 1]
+template <int C, class T>
+__global__ void __launch_bounds__(NT) k_first_wgrad(const T *__restrict__ g0, const float *__restrict__ x, double *__restrict__ dw0,
+                                                    int H, int W)
+{
+    constexpr int NV = C * 18;
+    __shared__ float scratch[(NT / 32) * NV * 32];
+    const int lane = threadIdx.x & 31, c0 = 2 * lane;
+    float acc[NV];
+#pragma unroll
+    for (int i = 0; i < NV; i++) acc[i] = 0.0f;
+    const size_t P = (size_t)H * W, nw = (size_t)gridDim.x * (NT / 32);
+    for (size_t p = (size_t)blockIdx.x * (NT / 32) + (threadIdx.x >> 5); p < P; p += nw) {
+        const int y = (int)(p / W), xx = (int)(p % W);
+        const float2 gg = St<T>::ld(g0 + p * 64 + c0);
+#pragma unroll
+        for (int tp = 0; tp < 9; tp++) {
+            const int yy = y + tp / 3 - 1, xq = xx + tp % 3 - 1;
+            const bool in = yy >= 0 && yy < H && xq >= 0 && xq < W;
+#pragma unroll
+            for (int ci = 0; ci < C; ci++) {
+                const float xv = in ? __ldg(x + ci * P + (size_t)yy * W + xq) : 0.0f;
+                acc[(ci * 9 + tp) * 2] = fmaf(gg.x, xv, acc[(ci * 9 + tp) * 2]);
+                acc[(ci * 9 + tp) * 2 + 1] = fmaf(gg.y, xv, acc[(ci * 9 + tp) * 2 + 1]);
+            }
+        }
+    }
+    block_lane_reduce<NV>(acc, scratch, [&](int l, int i) -> double * {
+        return dw0 + ((size_t)(2 * l + (i & 1)) * C + i / 18) * 9 + (i % 18) / 2;
+    });
+}
+
+static int bad_channels(int C)
+{
+    set_error("DnCNN channels = %d: the library is built for 1 (gray) and 3 (RGB) image channels", C);
+    return F2F_EINVAL;
+}
+static int gen_grid() { return sm_count() * 16; }
+template <class T>
+static int first_fwd(int C, const float *x, const float *w0, T *a0, int H, int W, cudaStream_t st)
+{
+    if (C == 1) k_first_fwd<1, T><<<gen_grid(), NT, 0, st>>>(x, w0, a0, H, W);
+    else if (C == 3) k_first_fwd<3, T><<<gen_grid(), NT, 0, st>>>(x, w0, a0, H, W);
+    else return bad_channels(C);
+    g_dncnn_launches++;
+    F2F_LAUNCH_CHECK();
+    return F2F_OK;
+}
+template <class T>
+static int last_fwd(int C, const T *z, const float *coef, const float *w16, const float *x, float *out, int H, int W,
+                    int residual, cudaStream_t st)
+{
+    if (C == 1) k_last_fwd<1, T><<<gen_grid(), NT, 0, st>>>(z, coef, w16, x, out, H, W, residual);
+    else if (C == 3) k_last_fwd<3, T><<<gen_grid(), NT, 0, st>>>(z, coef, w16, x, out, H, W, residual);
+    else return bad_channels(C);
+    g_dncnn_launches++;
+    F2F_LAUNCH_CHECK();
+    return F2F_OK;
+}
+template <class T>
+static int last_bwd(int C, const float *dy, float dy_sign, const T *z, const float *coef, const float *w16, T *g, double *stats,
+                    double *dw16, int H, int W, const unsigned *absmax, cudaStream_t st)
+{
+    if (C == 1) k_last_bwd<1, T><<<gen_grid(), NT, 0, st>>>(dy, dy_sign, z, coef, w16, g, stats, dw16, H, W, absmax);
+    else if (C == 3) k_last_bwd<3, T><<<gen_grid(), NT, 0, st>>>(dy, dy_sign, z, coef, w16, g, stats, dw16, H, W, absmax);
+    else return bad_channels(C);
+    g_dncnn_launches++;
+    F2F_LAUNCH_CHECK();
+    return F2F_OK;
+}
+template <class T>
+static int first_wgrad(int C, const T *g0, const float *x, double *dw0, int H, int W, cudaStream_t st)
+{
+    if (C == 1) k_first_wgrad<1, T><<<gen_grid(), NT, 0, st>>>(g0, x, dw0, H, W);
+    else if (C == 3) k_first_wgrad<3, T><<<gen_grid(), NT, 0, st>>>(g0, x, dw0, H, W);
+    else return bad_channels(C);
+    g_dncnn_launches++;
+    F2F_LAUNCH_CHECK();
+    return F2F_OK;
+}
+}  // namespace gen
 
 // ------------------------------------------------------- tcgen05 weight gradient
 // dW[oc][ic][ky][kx] = sum_p dz[p][oc] * a[p + (ky-1, kx-1)][ic]   (a = the layer's input activation)
@@ -743,14 +1040,14 @@ struct Plan {
 
 static int num_sms() { return sm_count(); }   // of the current device (f2f_common.cuh)
 
-static Plan make_plan(int B, int H, int W, int train)
+static Plan make_plan(int B, int H, int W, int train, int C = 1)
 {
     Plan p;
     const size_t P = (size_t)H * W;
     p.act_bytes = align_up((size_t)B * P * 128, 1024);
     size_t o = 0;
     auto take = [&](size_t bytes) { const size_t r = o; o += align_up(bytes, 1024); return r; };
-    p.o_x = take((size_t)B * P * 4);
+    p.o_x = take((size_t)B * P * 4 * C);
     p.o_a0 = take(p.act_bytes);
     p.nz = train ? NBN : 2;                       // eval: ping-pong
     p.o_z = take(p.act_bytes * p.nz);
@@ -759,7 +1056,7 @@ static Plan make_plan(int B, int H, int W, int train)
     p.o_wprep = take((size_t)30 * WSZ * 2);
     p.o_stats_f = take((size_t)NBN * 128 * 8);
     p.o_stats_b = take((size_t)NBN * 128 * 8);     // contiguous with o_dw_small: one memset
-    p.o_dw_small = take((size_t)1152 * 8);
+    p.o_dw_small = take((size_t)1152 * C * 8);
     p.o_absmax = take(16);                         // bits of max|dy| (gradient scaling); zeroed by the same memset
     p.o_coef = take((size_t)NBN * C_STRIDE * 4);
     p.o_partial = train ? take((size_t)num_sms() * wg::PARTIAL * 4) : 0;   // one partial per CTA of the persistent grid
@@ -785,16 +1082,18 @@ using namespace f2f::net;
 extern "C" {
 
 size_t f2f_dncnn_param_count(void) { return NPARAMS; }
+size_t f2f_dncnn_param_count_c(int channels) { return channels >= 1 ? NPARAMS + (size_t)2 * 576 * (channels - 1) : 0; }
 
 void f2f_dncnn_set_precise(int on) { g_precise = on != 0; }
 int f2f_dncnn_get_precise(void) { return g_precise; }
 
-size_t f2f_dncnn_workspace_bytes(int B, int H, int W, int train)
+size_t f2f_dncnn_workspace_bytes_c(int B, int H, int W, int train, int channels)
 {
-    if (B < 1 || H < 1 || W < 1) return 0;
-    if (g_precise) return pr::make_plan_f(B, H, W, train).total;
-    return make_plan(B, H, W, train).total;
+    if (B < 1 || H < 1 || W < 1 || channels < 1) return 0;
+    if (g_precise) return pr::make_plan_f(B, H, W, train, channels).total;
+    return make_plan(B, H, W, train, channels).total;
 }
+size_t f2f_dncnn_workspace_bytes(int B, int H, int W, int train) { return f2f_dncnn_workspace_bytes_c(B, H, W, train, 1); }
 
 void f2f_dncnn_set_debug_dump(void *d_buf) { g_debug_dump = d_buf; }
 
@@ -811,16 +1110,38 @@ void f2f_dncnn_workspace_layout(int B, int H, int W, int train, size_t out[8])
     out[6] = p.o_coef; out[7] = p.o_stats_f;
 }
 
+static int forward_impl(const float *d_params, float *d_bn_running, long long *d_nbt, const float *d_x, float *d_y,
+                        void *d_ws, size_t ws_bytes, int B, int H, int W, int train, int residual, void *stream,
+                        const rs::LossFuse *fuse, int C = 1);
+
 int f2f_dncnn_forward(const float *d_params, float *d_bn_running, long long *d_nbt, const float *d_x, float *d_y,
                       void *d_ws, size_t ws_bytes, int B, int H, int W, int train, int residual, void *stream)
+{
+    return forward_impl(d_params, d_bn_running, d_nbt, d_x, d_y, d_ws, ws_bytes, B, H, W, train, residual, stream, nullptr);
+}
+
+int f2f_dncnn_forward_c(const float *d_params, float *d_bn_running, long long *d_nbt, const float *d_x, float *d_y,
+                        void *d_ws, size_t ws_bytes, int B, int H, int W, int train, int residual, int channels, void *stream)
+{
+    if (channels != 1 && channels != 3) return gen::bad_channels(channels);
+    return forward_impl(d_params, d_bn_running, d_nbt, d_x, d_y, d_ws, ws_bytes, B, H, W, train, residual, stream, nullptr, channels);
+}
+
+// fuse != NULL (B = 1, default mode only): the loss of f2f_step_train is formed in the last layer's kernel; the caller has
+// zeroed *fuse->loss, and fuse->absmax (filled in here: the workspace's own word) is zeroed below
+static int forward_impl(const float *d_params, float *d_bn_running, long long *d_nbt, const float *d_x, float *d_y,
+                        void *d_ws, size_t ws_bytes, int B, int H, int W, int train, int residual, void *stream,
+                        const rs::LossFuse *fuse, int C)
 {
     if (!d_params || !d_bn_running || !d_x || !d_y || !d_ws || B < 1 || H < 1 || W < 1) {
         set_error("f2f_dncnn_forward: bad arguments");
         return F2F_EINVAL;
     }
     if (g_precise)
-        return pr::forward(d_params, d_bn_running, d_nbt, d_x, d_y, d_ws, ws_bytes, B, H, W, train, residual, (cudaStream_t)stream);
-    const Plan pl = make_plan(B, H, W, train);
+        return pr::forward(d_params, d_bn_running, d_nbt, d_x, d_y, d_ws, ws_bytes, B, H, W, train, residual, (cudaStream_t)stream, C);
+    const Plan pl = make_plan(B, H, W, train, C);
+    const float *d_w0 = d_params;
+    d_params += (size_t)576 * (C - 1);              // off_conv / off_gamma / off_beta / OFF_W16 are written for C = 1
     if (ws_bytes < pl.total) {
         set_error("f2f_dncnn_forward: workspace too small (%zu bytes, need %zu)", ws_bytes, pl.total);
         return F2F_ENOMEM;
@@ -838,14 +1159,19 @@ int f2f_dncnn_forward(const float *d_params, float *d_bn_running, long long *d_n
     g_dncnn_launches++;
     if (train) {
         F2F_CUDA_CHECK(cudaMemsetAsync(stats_f, 0, (size_t)NBN * 128 * 8, st));
-        F2F_CUDA_CHECK(cudaMemcpyAsync(ws + pl.o_x, d_x, (size_t)B * P * 4, cudaMemcpyDeviceToDevice, st));
+        F2F_CUDA_CHECK(cudaMemcpyAsync(ws + pl.o_x, d_x, (size_t)B * P * 4 * C, cudaMemcpyDeviceToDevice, st));
     } else {
         k_bn_eval_coeffs<<<NBN, 64, 0, st>>>(d_params, d_bn_running, coef);
         g_dncnn_launches++;
     }
     for (int b = 0; b < B; b++) {
+        if (C != 1) {
+            const int rc = gen::first_fwd<h16>(C, d_x + b * P * C, d_w0, a0 + b * P * 64, H, W, st);
+            if (rc) return rc;
+            continue;
+        }
         const int rtx = cdiv(W, rs::TW), rnt = rtx * cdiv(H, rs::TH);
-        rs::k_first_fwd<<<rnt < num_sms() * 6 ? rnt : num_sms() * 6, rs::FT, 0, st>>>(d_x + b * P, d_params + OFF_W0,
+        rs::k_first_fwd<<<rnt < num_sms() * 6 ? rnt : num_sms() * 6, rs::FT, 0, st>>>(d_x + b * P, d_w0,
                                                                                     a0 + b * P * 64, H, W, rtx, rnt);
         g_dncnn_launches++;
     }
@@ -868,10 +1194,22 @@ int f2f_dncnn_forward(const float *d_params, float *d_bn_running, long long *d_n
         }
     }
     const int tiles_x = cdiv(W, LT), ntiles = tiles_x * cdiv(H, LT);
+    rs::LossFuse lf = {};
+    if (fuse && train && B == 1) {
+        lf = *fuse;
+        lf.absmax = (unsigned *)(ws + pl.o_absmax);
+        F2F_CUDA_CHECK(cudaMemsetAsync(lf.absmax, 0, 16, st));
+    }
     for (int b = 0; b < B; b++) {
+        if (C != 1) {
+            const int rc = gen::last_fwd<h16>(C, zbuf(NBN) + b * P * 64, coef + (size_t)(NBN - 1) * C_STRIDE, d_params + OFF_W16,
+                                              d_x + b * P * C, d_y + b * P * C, H, W, residual, st);
+            if (rc) return rc;
+            continue;
+        }
         rs::k_last_fwd<<<ntiles < simt_blocks() ? ntiles : simt_blocks(), 256, 0, st>>>(
             zbuf(NBN) + b * P * 64, coef + (size_t)(NBN - 1) * C_STRIDE, d_params + OFF_W16, d_x + b * P, d_y + b * P, H, W,
-            tiles_x, ntiles, residual);
+            tiles_x, ntiles, residual, lf);
         g_dncnn_launches++;
     }
     F2F_LAUNCH_CHECK();
@@ -914,16 +1252,36 @@ static int wgrad64_scaled(const void *d_act, const float *d_coef_in, void *d_g, 
     return F2F_OK;
 }
 
+static int backward_impl(const float *d_params, float *d_grads, const float *d_dy, void *d_ws, size_t ws_bytes, int B, int H,
+                         int W, int residual, int accumulate, void *stream, int absmax_ready, int C = 1);
+
 int f2f_dncnn_backward(const float *d_params, float *d_grads, const float *d_dy, void *d_ws, size_t ws_bytes, int B, int H,
                        int W, int residual, int accumulate, void *stream)
+{
+    return backward_impl(d_params, d_grads, d_dy, d_ws, ws_bytes, B, H, W, residual, accumulate, stream, 0);
+}
+
+int f2f_dncnn_backward_c(const float *d_params, float *d_grads, const float *d_dy, void *d_ws, size_t ws_bytes, int B, int H,
+                         int W, int residual, int accumulate, int channels, void *stream)
+{
+    if (channels != 1 && channels != 3) return gen::bad_channels(channels);
+    return backward_impl(d_params, d_grads, d_dy, d_ws, ws_bytes, B, H, W, residual, accumulate, stream, 0, channels);
+}
+
+// absmax_ready: max|dy| already sits in the workspace (written by the fused last-layer kernel of forward_impl)
+static int backward_impl(const float *d_params, float *d_grads, const float *d_dy, void *d_ws, size_t ws_bytes, int B, int H,
+                         int W, int residual, int accumulate, void *stream, int absmax_ready, int C)
 {
     if (!d_params || !d_grads || !d_dy || !d_ws || B < 1 || H < 1 || W < 1) {
         set_error("f2f_dncnn_backward: bad arguments");
         return F2F_EINVAL;
     }
     if (g_precise)
-        return pr::backward(d_params, d_grads, d_dy, d_ws, ws_bytes, B, H, W, residual, accumulate, (cudaStream_t)stream);
-    const Plan pl = make_plan(B, H, W, 1);
+        return pr::backward(d_params, d_grads, d_dy, d_ws, ws_bytes, B, H, W, residual, accumulate, (cudaStream_t)stream, C);
+    const Plan pl = make_plan(B, H, W, 1, C);
+    float *d_gw0 = d_grads;
+    d_params += (size_t)576 * (C - 1);
+    d_grads += (size_t)576 * (C - 1);
     if (ws_bytes < pl.total) {
         set_error("f2f_dncnn_backward: workspace too small (%zu bytes, need %zu)", ws_bytes, pl.total);
         return F2F_ENOMEM;
@@ -937,7 +1295,7 @@ int f2f_dncnn_backward(const float *d_params, float *d_grads, const float *d_dy,
     const h16 *wprep = (const h16 *)(ws + pl.o_wprep);
     float *coef = (float *)(ws + pl.o_coef);
     double *stats_b = (double *)(ws + pl.o_stats_b);
-    double *dw0 = (double *)(ws + pl.o_dw_small), *dw16 = dw0 + 576;
+    double *dw0 = (double *)(ws + pl.o_dw_small), *dw16 = dw0 + 576 * C;
     const float *x = (const float *)(ws + pl.o_x);
     h16 *a0 = (h16 *)(ws + pl.o_a0);
     float *partial = (float *)(ws + pl.o_partial);
@@ -946,12 +1304,21 @@ int f2f_dncnn_backward(const float *d_params, float *d_grads, const float *d_dy,
 
     // stats_b and the small double accumulators are adjacent (make_plan)
     unsigned *absmax = (unsigned *)(ws + pl.o_absmax);
-    F2F_CUDA_CHECK(cudaMemsetAsync(stats_b, 0, (pl.o_absmax - pl.o_stats_b) + 16, st));
-    k_absmax<<<num_sms(), 256, 0, st>>>(d_dy, (size_t)B * P, absmax);      // gradient scaling, see grad_scale()
-    g_dncnn_launches++;
+    F2F_CUDA_CHECK(cudaMemsetAsync(stats_b, 0, (pl.o_absmax - pl.o_stats_b) + (absmax_ready ? 0 : 16), st));
+    if (!absmax_ready) {
+        k_absmax<<<num_sms(), 256, 0, st>>>(d_dy, (size_t)B * P * C, absmax);      // gradient scaling, see grad_scale()
+        g_dncnn_launches++;
+    }
     int cur = 0;   // gbuf[cur] holds g_k
     const int rtx = cdiv(W, rs::TW), rnt = rtx * cdiv(H, rs::TH);
     for (int b = 0; b < B; b++) {
+        if (C != 1) {
+            const int rc = gen::last_bwd<h16>(C, d_dy + b * P * C, residual ? -1.0f : 1.0f, zbuf(NBN) + b * P * 64,
+                                              coef + (size_t)(NBN - 1) * C_STRIDE, d_params + OFF_W16, gbuf[cur] + b * P * 64,
+                                              stats_b + (size_t)(NBN - 1) * 128, dw16, H, W, absmax, st);
+            if (rc) return rc;
+            continue;
+        }
         rs::k_last_bwd<<<rnt < num_sms() ? rnt : num_sms(), rs::NT, rs::SMEM, st>>>(
             d_dy + b * P, residual ? -1.0f : 1.0f, zbuf(NBN) + b * P * 64, coef + (size_t)(NBN - 1) * C_STRIDE,
             d_params + OFF_W16, gbuf[cur] + b * P * 64, stats_b + (size_t)(NBN - 1) * 128, dw16, H, W, rtx, rnt, absmax);
@@ -989,11 +1356,16 @@ int f2f_dncnn_backward(const float *d_params, float *d_grads, const float *d_dy,
     }
     dump(30, gbuf[cur]);
     for (int b = 0; b < B; b++) {
+        if (C != 1) {
+            const int rc = gen::first_wgrad<h16>(C, gbuf[cur] + b * P * 64, x + b * P * C, dw0, H, W, st);
+            if (rc) return rc;
+            continue;
+        }
         rs::k_first_wgrad<<<rnt < num_sms() ? rnt : num_sms(), rs::NT, rs::SMEM, st>>>(gbuf[cur] + b * P * 64, x + b * P, dw0, H,
                                                                                        W, rtx, rnt);
         g_dncnn_launches++;
     }
-    k_small_grads<<<cdiv(1152, 256), 256, 0, st>>>(dw0, dw16, d_grads, accumulate, absmax);
+    k_small_grads<<<cdiv(1152 * C, 256), 256, 0, st>>>(dw0, dw16, d_gw0, d_grads + OFF_W16, 576 * C, accumulate, absmax);
     g_dncnn_launches++;
     F2F_LAUNCH_CHECK();
     return F2F_OK;
@@ -1026,8 +1398,23 @@ int f2f_step_train(float *d_params, float *d_grads, float *d_m, float *d_v, floa
                    double *d_loss, void *d_ws, size_t ws_bytes, int H, int W, int loss_kind, long long step, float lr,
                    float beta1, float beta2, float eps, float weight_decay, void *stream)
 {
-    if (!d_out || !d_dout || !d_loss) { set_error("f2f_step_train: bad arguments"); return F2F_EINVAL; }
-    int rc = f2f_dncnn_forward(d_params, d_bn_running, d_nbt, d_curr, d_out, d_ws, ws_bytes, 1, H, W, 1, 1, stream);
+    if (!d_out || !d_dout || !d_loss || !d_warped || !d_mask || loss_kind < 0 || loss_kind > 2) {
+        set_error("f2f_step_train: bad arguments");
+        return F2F_EINVAL;
+    }
+    int rc;
+    static const int fuse_loss = getenv("F2F_FUSE_LOSS") ? atoi(getenv("F2F_FUSE_LOSS")) : 1;
+    if (!g_precise && fuse_loss) {
+        // masked loss, its gradient and max|gradient| in the last layer's kernel (rs::LossFuse)
+        rs::LossFuse lf = {d_warped, d_mask, d_dout, d_loss, nullptr, loss_kind, 1.0f / (float)((size_t)H * W)};
+        F2F_CUDA_CHECK(cudaMemsetAsync(d_loss, 0, sizeof(double), (cudaStream_t)stream));
+        rc = forward_impl(d_params, d_bn_running, d_nbt, d_curr, d_out, d_ws, ws_bytes, 1, H, W, 1, 1, stream, &lf);
+        if (rc) return rc;
+        rc = backward_impl(d_params, d_grads, d_dout, d_ws, ws_bytes, 1, H, W, 1, 0, stream, 1);
+        if (rc) return rc;
+        return f2f_adam_step(d_params, d_grads, d_m, d_v, NPARAMS, step, lr, beta1, beta2, eps, weight_decay, stream);
+    }
+    rc = f2f_dncnn_forward(d_params, d_bn_running, d_nbt, d_curr, d_out, d_ws, ws_bytes, 1, H, W, 1, 1, stream);
     if (rc) return rc;
     rc = f2f_masked_loss(d_out, d_warped, d_mask, d_dout, d_loss, (size_t)H * W, loss_kind, stream);
     if (rc) return rc;

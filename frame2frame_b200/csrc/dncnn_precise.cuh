@@ -265,139 +265,6 @@ __global__ void k_wgrad_reduce_f(const float *__restrict__ partial, int nparts, 
     *d = (accumulate ? *d : 0.0f) + s;
 }
 
-// ---------------------------------------------------------------- first / last layer (a warp per pixel, a lane = 2 channels)
-__global__ void k_first_fwd_f(const float *__restrict__ x, const float *__restrict__ w0, float *__restrict__ a0, int H, int W)
-{
-    const int lane = threadIdx.x & 31, c0 = 2 * lane;
-    float w[9][2];
-#pragma unroll
-    for (int tp = 0; tp < 9; tp++) { w[tp][0] = w0[c0 * 9 + tp]; w[tp][1] = w0[(c0 + 1) * 9 + tp]; }
-    const size_t P = (size_t)H * W, nw = (size_t)gridDim.x * (blockDim.x >> 5);
-    for (size_t p = (size_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); p < P; p += nw) {
-        const int y = (int)(p / W), xx = (int)(p % W);
-        float s0 = 0.0f, s1 = 0.0f;
-#pragma unroll
-        for (int tp = 0; tp < 9; tp++) {
-            const int yy = y + tp / 3 - 1, xq = xx + tp % 3 - 1;
-            const float v = (yy >= 0 && yy < H && xq >= 0 && xq < W) ? __ldg(x + (size_t)yy * W + xq) : 0.0f;
-            s0 = fmaf(v, w[tp][0], s0); s1 = fmaf(v, w[tp][1], s1);
-        }
-        *reinterpret_cast<float2 *>(a0 + p * 64 + c0) = make_float2(fmaxf(s0, 0.0f), fmaxf(s1, 0.0f));
-    }
-}
-
-__global__ void k_last_fwd_f(const float *__restrict__ z, const float *__restrict__ coef, const float *__restrict__ w16,
-                             const float *__restrict__ x, float *__restrict__ out, int H, int W, int residual)
-{
-    const int lane = threadIdx.x & 31, c0 = 2 * lane;
-    float w[9][2];
-#pragma unroll
-    for (int tp = 0; tp < 9; tp++) { w[tp][0] = w16[c0 * 9 + tp]; w[tp][1] = w16[(c0 + 1) * 9 + tp]; }
-    const float sc0 = coef[C_SCALE + c0], sc1 = coef[C_SCALE + c0 + 1], sh0 = coef[C_SHIFT + c0], sh1 = coef[C_SHIFT + c0 + 1];
-    const size_t P = (size_t)H * W, nw = (size_t)gridDim.x * (blockDim.x >> 5);
-    for (size_t p = (size_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); p < P; p += nw) {
-        const int y = (int)(p / W), xx = (int)(p % W);
-        float s = 0.0f;
-#pragma unroll
-        for (int tp = 0; tp < 9; tp++) {
-            const int yy = y + tp / 3 - 1, xq = xx + tp % 3 - 1;
-            if (yy >= 0 && yy < H && xq >= 0 && xq < W) {
-                const float2 zz = __ldg(reinterpret_cast<const float2 *>(z + ((size_t)yy * W + xq) * 64 + c0));
-                s = fmaf(fmaxf(fmaf(zz.x, sc0, sh0), 0.0f), w[tp][0], s);
-                s = fmaf(fmaxf(fmaf(zz.y, sc1, sh1), 0.0f), w[tp][1], s);
-            }
-        }
-        s = warp_sum(s);
-        if (lane == 0) out[p] = residual ? x[p] - s : s;
-    }
-}
-
-// sums NV per-lane values over the warps of a block and adds them to FP64 accumulators chosen by dst(lane, i)
-template <int NV, class F>
-__device__ __forceinline__ void block_lane_reduce(const float (&v)[NV], float *scratch, F dst)
-{
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
-#pragma unroll
-    for (int i = 0; i < NV; i++) scratch[(warp * NV + i) * 32 + lane] = v[i];
-    __syncthreads();
-    for (int e = threadIdx.x; e < 32 * NV; e += blockDim.x) {
-        const int i = e >> 5, l = e & 31;
-        double tsum = 0.0;
-        for (int w = 0; w < nwarp; w++) tsum += (double)scratch[(w * NV + i) * 32 + l];
-        atomicAdd(dst(l, i), tsum);
-    }
-}
-
-// Backward of the last layer: g15 = relu'(.) * conv^T(dn, w16), its BatchNorm-backward sums, and dW16 -- one pass over z15.
-__global__ void __launch_bounds__(256) k_last_bwd_f(const float *__restrict__ dy, float dy_sign, const float *__restrict__ z,
-                                                    const float *__restrict__ coef, const float *__restrict__ w16,
-                                                    float *__restrict__ g, double *__restrict__ stats, double *__restrict__ dw16,
-                                                    int H, int W)
-{
-    __shared__ float scratch[8 * 22 * 32];
-    const int lane = threadIdx.x & 31, c0 = 2 * lane;
-    float w[9][2], sc[2], sh[2], is[2], ms[2];
-#pragma unroll
-    for (int j = 0; j < 2; j++) {
-#pragma unroll
-        for (int tp = 0; tp < 9; tp++) w[tp][j] = w16[(c0 + j) * 9 + tp];
-        sc[j] = coef[C_SCALE + c0 + j]; sh[j] = coef[C_SHIFT + c0 + j];
-        is[j] = coef[C_INVSTD + c0 + j]; ms[j] = -coef[C_MEAN + c0 + j] * is[j];
-    }
-    float acc[22];
-#pragma unroll
-    for (int i = 0; i < 22; i++) acc[i] = 0.0f;
-    const size_t P = (size_t)H * W, nw = (size_t)gridDim.x * (blockDim.x >> 5);
-    for (size_t p = (size_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); p < P; p += nw) {
-        const int y = (int)(p / W), xx = (int)(p % W);
-        const float2 zz = __ldg(reinterpret_cast<const float2 *>(z + p * 64 + c0));
-        const float y0 = fmaf(zz.x, sc[0], sh[0]), y1 = fmaf(zz.y, sc[1], sh[1]);
-        const float a0 = fmaxf(y0, 0.0f), a1 = fmaxf(y1, 0.0f);
-        float s0 = 0.0f, s1 = 0.0f;
-#pragma unroll
-        for (int tp = 0; tp < 9; tp++) {
-            // dn at the OUTPUT pixel that tap tp of the forward conv maps to this input pixel: q = p - (tap offset)
-            const int yy = y - (tp / 3 - 1), xq = xx - (tp % 3 - 1);
-            const float dn = (yy >= 0 && yy < H && xq >= 0 && xq < W) ? dy_sign * __ldg(dy + (size_t)yy * W + xq) : 0.0f;
-            s0 = fmaf(dn, w[tp][0], s0); s1 = fmaf(dn, w[tp][1], s1);
-            acc[2 * tp] = fmaf(a0, dn, acc[2 * tp]); acc[2 * tp + 1] = fmaf(a1, dn, acc[2 * tp + 1]);
-        }
-        const float g0 = y0 > 0.0f ? s0 : 0.0f, g1 = y1 > 0.0f ? s1 : 0.0f;
-        *reinterpret_cast<float2 *>(g + p * 64 + c0) = make_float2(g0, g1);
-        acc[18] += g0; acc[19] += g1;
-        acc[20] = fmaf(g0, fmaf(zz.x, is[0], ms[0]), acc[20]);
-        acc[21] = fmaf(g1, fmaf(zz.y, is[1], ms[1]), acc[21]);
-    }
-    block_lane_reduce<22>(acc, scratch, [&](int l, int i) -> double * {
-        if (i < 18) return dw16 + (2 * l + (i & 1)) * 9 + (i >> 1);
-        if (i < 20) return stats + 2 * l + (i - 18);
-        return stats + 64 + 2 * l + (i - 20);
-    });
-}
-
-// dW0[oc][tap] = sum_p g0[p][oc] * x[p + tap - 1]
-__global__ void __launch_bounds__(256) k_first_wgrad_f(const float *__restrict__ g0, const float *__restrict__ x,
-                                                       double *__restrict__ dw0, int H, int W)
-{
-    __shared__ float scratch[8 * 18 * 32];
-    const int lane = threadIdx.x & 31, c0 = 2 * lane;
-    float acc[18];
-#pragma unroll
-    for (int i = 0; i < 18; i++) acc[i] = 0.0f;
-    const size_t P = (size_t)H * W, nw = (size_t)gridDim.x * (blockDim.x >> 5);
-    for (size_t p = (size_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); p < P; p += nw) {
-        const int y = (int)(p / W), xx = (int)(p % W);
-        const float2 gg = __ldg(reinterpret_cast<const float2 *>(g0 + p * 64 + c0));
-#pragma unroll
-        for (int tp = 0; tp < 9; tp++) {
-            const int yy = y + tp / 3 - 1, xq = xx + tp % 3 - 1;
-            const float xv = (yy >= 0 && yy < H && xq >= 0 && xq < W) ? __ldg(x + (size_t)yy * W + xq) : 0.0f;
-            acc[2 * tp] = fmaf(gg.x, xv, acc[2 * tp]); acc[2 * tp + 1] = fmaf(gg.y, xv, acc[2 * tp + 1]);
-        }
-    }
-    block_lane_reduce<18>(acc, scratch, [&](int l, int i) -> double * { return dw0 + (2 * l + (i & 1)) * 9 + (i >> 1); });
-}
-
 // ---------------------------------------------------------------- workspace plan and drivers
 struct PlanF {
     size_t act_bytes;
@@ -405,14 +272,14 @@ struct PlanF {
     int nz;
 };
 
-static PlanF make_plan_f(int B, int H, int W, int train)
+static PlanF make_plan_f(int B, int H, int W, int train, int C = 1)
 {
     PlanF p;
     const size_t P = (size_t)H * W;
     p.act_bytes = align_up((size_t)B * P * 256, 1024);
     size_t o = 0;
     auto take = [&](size_t bytes) { const size_t r = o; o += align_up(bytes, 1024); return r; };
-    p.o_x = take((size_t)B * P * 4);
+    p.o_x = take((size_t)B * P * 4 * C);
     p.o_a0 = take(p.act_bytes);
     p.nz = train ? NBN : 2;
     p.o_z = take(p.act_bytes * p.nz);
@@ -422,7 +289,7 @@ static PlanF make_plan_f(int B, int H, int W, int train)
     p.o_wprep = take((size_t)30 * WSZ * 4);
     p.o_stats_f = take((size_t)NBN * 128 * 8);
     p.o_stats_b = take((size_t)NBN * 128 * 8);     // contiguous with o_dw_small: one memset
-    p.o_dw_small = take((size_t)1152 * 8);
+    p.o_dw_small = take((size_t)1152 * C * 8);
     p.o_coef = take((size_t)NBN * C_STRIDE * 4);
     p.o_partial = train ? take((size_t)3 * num_sms() * WG_PARTIAL * 4) : 0;
     p.total = o;
@@ -443,9 +310,11 @@ static int launch_conv(ConvF a, cudaStream_t st)
 }
 
 static int forward(const float *d_params, float *d_bn_running, long long *d_nbt, const float *d_x, float *d_y, void *d_ws,
-                   size_t ws_bytes, int B, int H, int W, int train, int residual, cudaStream_t st)
+                   size_t ws_bytes, int B, int H, int W, int train, int residual, cudaStream_t st, int C)
 {
-    const PlanF pl = make_plan_f(B, H, W, train);
+    const PlanF pl = make_plan_f(B, H, W, train, C);
+    const float *d_w0 = d_params;
+    d_params += (size_t)576 * (C - 1);              // off_conv / off_gamma / off_beta / OFF_W16 are written for C = 1
     if (ws_bytes < pl.total) {
         set_error("f2f_dncnn_forward (precise): workspace too small (%zu bytes, need %zu)", ws_bytes, pl.total);
         return F2F_ENOMEM;
@@ -459,15 +328,14 @@ static int forward(const float *d_params, float *d_bn_running, long long *d_nbt,
     g_dncnn_launches++;
     if (train) {
         F2F_CUDA_CHECK(cudaMemsetAsync(stats_f, 0, (size_t)NBN * 128 * 8, st));
-        F2F_CUDA_CHECK(cudaMemcpyAsync(ws + pl.o_x, d_x, (size_t)B * P * 4, cudaMemcpyDeviceToDevice, st));
+        F2F_CUDA_CHECK(cudaMemcpyAsync(ws + pl.o_x, d_x, (size_t)B * P * 4 * C, cudaMemcpyDeviceToDevice, st));
     } else {
         k_bn_eval_coeffs<<<NBN, 64, 0, st>>>(d_params, d_bn_running, coef);
         g_dncnn_launches++;
     }
-    const int simt = num_sms() * 8;
     for (int b = 0; b < B; b++) {
-        k_first_fwd_f<<<simt, 256, 0, st>>>(d_x + b * P, d_params + OFF_W0, a0 + b * P * 64, H, W);
-        g_dncnn_launches++;
+        const int rc = gen::first_fwd<float>(C, d_x + b * P * C, d_w0, a0 + b * P * 64, H, W, st);
+        if (rc) return rc;
     }
     F2F_LAUNCH_CHECK();
     for (int k = 1; k <= NBN; k++) {
@@ -492,18 +360,20 @@ static int forward(const float *d_params, float *d_bn_running, long long *d_nbt,
         }
     }
     for (int b = 0; b < B; b++) {
-        k_last_fwd_f<<<simt, 256, 0, st>>>(zbuf(NBN) + b * P * 64, coef + (size_t)(NBN - 1) * C_STRIDE, d_params + OFF_W16,
-                                           d_x + b * P, d_y + b * P, H, W, residual);
-        g_dncnn_launches++;
+        const int rc = gen::last_fwd<float>(C, zbuf(NBN) + b * P * 64, coef + (size_t)(NBN - 1) * C_STRIDE, d_params + OFF_W16,
+                                            d_x + b * P * C, d_y + b * P * C, H, W, residual, st);
+        if (rc) return rc;
     }
-    F2F_LAUNCH_CHECK();
     return F2F_OK;
 }
 
 static int backward(const float *d_params, float *d_grads, const float *d_dy, void *d_ws, size_t ws_bytes, int B, int H, int W,
-                    int residual, int accumulate, cudaStream_t st)
+                    int residual, int accumulate, cudaStream_t st, int C)
 {
-    const PlanF pl = make_plan_f(B, H, W, 1);
+    const PlanF pl = make_plan_f(B, H, W, 1, C);
+    float *d_gw0 = d_grads;
+    d_params += (size_t)576 * (C - 1);
+    d_grads += (size_t)576 * (C - 1);
     if (ws_bytes < pl.total) {
         set_error("f2f_dncnn_backward (precise): workspace too small (%zu bytes, need %zu)", ws_bytes, pl.total);
         return F2F_ENOMEM;
@@ -515,21 +385,19 @@ static int backward(const float *d_params, float *d_grads, const float *d_dy, vo
     const float *wprep = (const float *)(ws + pl.o_wprep);
     float *coef = (float *)(ws + pl.o_coef);
     double *stats_b = (double *)(ws + pl.o_stats_b);
-    double *dw0 = (double *)(ws + pl.o_dw_small), *dw16 = dw0 + 576;
+    double *dw0 = (double *)(ws + pl.o_dw_small), *dw16 = dw0 + 576 * C;
     const float *x = (const float *)(ws + pl.o_x);
     float *a0 = (float *)(ws + pl.o_a0), *partial = (float *)(ws + pl.o_partial), *dz = (float *)(ws + pl.o_dz);
     auto zbuf = [&](int k) { return (float *)(ws + pl.o_z + pl.act_bytes * (size_t)(k - 1)); };
     float *gbuf[2] = {(float *)(ws + pl.o_g0), (float *)(ws + pl.o_g1)};
-    F2F_CUDA_CHECK(cudaMemsetAsync(stats_b, 0, (pl.o_dw_small - pl.o_stats_b) + (size_t)1152 * 8, st));
-    const int simt = num_sms() * 8;
+    F2F_CUDA_CHECK(cudaMemsetAsync(stats_b, 0, (pl.o_dw_small - pl.o_stats_b) + (size_t)1152 * C * 8, st));
     int cur = 0;
     for (int b = 0; b < B; b++) {
-        k_last_bwd_f<<<simt, 256, 0, st>>>(d_dy + b * P, residual ? -1.0f : 1.0f, zbuf(NBN) + b * P * 64,
-                                           coef + (size_t)(NBN - 1) * C_STRIDE, d_params + OFF_W16, gbuf[cur] + b * P * 64,
-                                           stats_b + (size_t)(NBN - 1) * 128, dw16, H, W);
-        g_dncnn_launches++;
+        const int rc = gen::last_bwd<float>(C, d_dy + b * P * C, residual ? -1.0f : 1.0f, zbuf(NBN) + b * P * 64,
+                                            coef + (size_t)(NBN - 1) * C_STRIDE, d_params + OFF_W16, gbuf[cur] + b * P * 64,
+                                            stats_b + (size_t)(NBN - 1) * 128, dw16, H, W, nullptr, st);
+        if (rc) return rc;
     }
-    F2F_LAUNCH_CHECK();
     const int tiles_x = cdiv(W, TC), ntiles = tiles_x * cdiv(H, TR);
     const int wg_grid = ntiles < num_sms() ? ntiles : num_sms();
     for (int k = NBN; k >= 1; k--) {
@@ -558,10 +426,10 @@ static int backward(const float *d_params, float *d_grads, const float *d_dy, vo
         cur ^= 1;
     }
     for (int b = 0; b < B; b++) {
-        k_first_wgrad_f<<<simt, 256, 0, st>>>(gbuf[cur] + b * P * 64, x + b * P, dw0, H, W);
-        g_dncnn_launches++;
+        const int rc = gen::first_wgrad<float>(C, gbuf[cur] + b * P * 64, x + b * P * C, dw0, H, W, st);
+        if (rc) return rc;
     }
-    k_small_grads<<<cdiv(1152, 256), 256, 0, st>>>(dw0, dw16, d_grads, accumulate, (const unsigned *)nullptr);
+    k_small_grads<<<cdiv(1152 * C, 256), 256, 0, st>>>(dw0, dw16, d_gw0, d_grads + OFF_W16, 576 * C, accumulate, (const unsigned *)nullptr);
     g_dncnn_launches++;
     F2F_LAUNCH_CHECK();
     return F2F_OK;

@@ -48,10 +48,10 @@ class _Workspace:
         self.key = None
         self.buf = None
 
-    def get(self, B, H, W, train, device):
-        key = (B, H, W, bool(train), str(device), lib().f2f_dncnn_get_precise())
+    def get(self, B, H, W, train, device, channels=1):
+        key = (B, H, W, bool(train), str(device), lib().f2f_dncnn_get_precise(), channels)
         if self.key != key:
-            n = lib().f2f_dncnn_workspace_bytes(B, H, W, int(train))
+            n = lib().f2f_dncnn_workspace_bytes_c(B, H, W, int(train), channels)
             if n == 0:
                 raise ValueError("bad DnCNN geometry B=%d H=%d W=%d" % (B, H, W))
             self.buf = None
@@ -69,12 +69,12 @@ class _DnCNNFunction(torch.autograd.Function):
         B, C, H, W = x.shape
         train = model.training
         ws = model._ws_train if train else model._ws_eval
-        buf = ws.get(B, H, W, train, x.device)
+        buf = ws.get(B, H, W, train, x.device, C)
         y = torch.empty_like(x)
         with torch.cuda.device(x.device):
-            check(lib().f2f_dncnn_forward(flat.data_ptr(), model._running.data_ptr(), model._nbt.data_ptr(),
-                                          x.data_ptr(), y.data_ptr(), buf.data_ptr(), buf.numel(), B, H, W,
-                                          int(train), int(model.residual), _stream()), "f2f_dncnn_forward")
+            check(lib().f2f_dncnn_forward_c(flat.data_ptr(), model._running.data_ptr(), model._nbt.data_ptr(),
+                                            x.data_ptr(), y.data_ptr(), buf.data_ptr(), buf.numel(), B, H, W,
+                                            int(train), int(model.residual), C, _stream()), "f2f_dncnn_forward")
         ctx.model, ctx.geom, ctx.train = model, (B, H, W), train
         if train:
             model._fwd_id += 1
@@ -89,13 +89,13 @@ class _DnCNNFunction(torch.autograd.Function):
         if ctx.fwd_id != model._fwd_id:
             raise RuntimeError("DnCNN backward: the workspace was overwritten by a later forward pass")
         B, H, W = ctx.geom
-        buf = model._ws_train.get(B, H, W, True, dy.device)
+        buf = model._ws_train.get(B, H, W, True, dy.device, model.channels)
         accumulate = model._grads_attached()
         dy = dy.contiguous().float()
         with torch.cuda.device(dy.device):
-            check(lib().f2f_dncnn_backward(model._flat.data_ptr(), model._flat_grad.data_ptr(), dy.data_ptr(),
-                                           buf.data_ptr(), buf.numel(), B, H, W, int(model.residual), int(accumulate),
-                                           _stream()), "f2f_dncnn_backward")
+            check(lib().f2f_dncnn_backward_c(model._flat.data_ptr(), model._flat_grad.data_ptr(), dy.data_ptr(),
+                                             buf.data_ptr(), buf.numel(), B, H, W, int(model.residual), int(accumulate),
+                                             model.channels, _stream()), "f2f_dncnn_backward")
         model._attach_grads()
         return None, None, None
 
@@ -107,10 +107,10 @@ class DnCNN(nn.Module):
 
     def __init__(self, channels=1, num_of_layers=17, residual=True):
         super().__init__()
-        if channels != 1 or num_of_layers != 17:
-            raise NotImplementedError("the B200 kernels are built for the DnCNN-S grayscale model "
-                                      "(channels=1, num_of_layers=17), got channels=%d, num_of_layers=%d"
-                                      % (channels, num_of_layers))
+        if channels not in (1, 3) or num_of_layers != 17:
+            raise NotImplementedError("the B200 kernels are built for the 17-layer DnCNN with 1 (gray) or 3 (RGB) image "
+                                      "channels, got channels=%d, num_of_layers=%d" % (channels, num_of_layers))
+        self.channels = channels
         kernel_size, padding, features = 3, 1, FEATURES
         layers = [nn.Conv2d(channels, features, kernel_size, padding=padding, bias=False), nn.ReLU(inplace=True)]
         for _ in range(num_of_layers - 2):
@@ -141,7 +141,7 @@ class DnCNN(nn.Module):
         dev = params[0].device
         with torch.no_grad():
             flat = torch.cat([p.detach().reshape(-1).float() for p in params]).to(dev).contiguous()
-            assert flat.numel() == NPARAMS
+            assert flat.numel() == NPARAMS + 1152 * (self.channels - 1)
             running = torch.stack([torch.stack([b.running_mean.float(), b.running_var.float()]) for b in bns]).to(dev).contiguous()
             nbt = torch.stack([b.num_batches_tracked.reshape(()).long() for b in bns]).to(dev).contiguous()
         flat.requires_grad_(True)
@@ -213,8 +213,8 @@ class DnCNN(nn.Module):
             shape5 = x.shape
             x = x.reshape(-1, *x.shape[2:])
         x = x.contiguous().float()
-        if x.shape[1] != 1:
-            raise ValueError("expected a 1-channel input, got %s" % (tuple(x.shape),))
+        if x.shape[1] != self.channels:
+            raise ValueError("expected a %d-channel input, got %s" % (self.channels, tuple(x.shape)))
         y = _DnCNNFunction.apply(x, self._flat, self)
         if shape5 is not None:
             y = y.reshape(shape5)

@@ -4,9 +4,9 @@
 call the CUDA path.  The reference's config plumbing (``dev_basics.configs.ExtractConfig``) is an un-vendored
 dependency; its observable behaviour for this model is restated: keys, defaults, ``restrict`` filtering.
 
-Differences, stated rather than hidden: only ``channels == 1`` is implemented (north_star's grayscale DnCNN; the
-reference default of 3 raises), and ``net_name`` values of the FastDVDnet family raise ``ValueError`` like any unknown
-name (that model is outside SURVEY section 8).
+Differences, stated rather than hidden: ``channels`` is 1 (north_star's grayscale DnCNN) or 3 (the reference's default,
+dncnn/io.py:64-67) -- other counts raise; ``net_name`` values of the FastDVDnet family raise ``ValueError`` like any
+unknown name (that model is outside SURVEY section 8).
 """
 import torch
 
@@ -63,8 +63,9 @@ def load_model(cfg):
     in-tree forward convention ``x - dncnn(x)`` (net.py:31), optional checkpoint, moved to cfg.device."""
     c = extract_config(cfg)
     print("load_model:", c["net_name"])
-    if int(c["channels"]) != 1:
-        raise NotImplementedError("frame2frame_b200 implements the 1-channel (grayscale) DnCNN; got channels=%r" % (c["channels"],))
+    if int(c["channels"]) not in (1, 3):
+        raise NotImplementedError("frame2frame_b200 implements the DnCNN for 1 (gray) or 3 (RGB) image channels; got channels=%r"
+                                  % (c["channels"],))
     model = DnCNN(int(c["channels"]), int(c["num_of_layers"]), residual=True)
     load_pretrained(model, c)
     return model.to(c["device"])

@@ -268,6 +268,19 @@ int f2f_dncnn_forward(const float *d_params, float *d_bn_running, long long *d_n
 int f2f_dncnn_backward(const float *d_params, float *d_grads, const float *d_dy, void *d_ws,
                        size_t ws_bytes, int B, int H, int W, int residual, int accumulate,
                        void *stream);
+/* The same for a network with `channels` image channels (1 or 3; the reference's loader defaults to 3,
+ * lib/frame2frame/dncnn/io.py:64-67): d_x, d_y, d_dy are [B][channels][H][W] FP32 (NCHW like the reference's tensors),
+ * the flat parameter / gradient vectors have f2f_dncnn_param_count_c(channels) = 556032 + 1152 * (channels - 1) floats
+ * (conv0.weight [64][channels][3][3] first, conv16.weight [channels][64][3][3] last).  channels = 1 is exactly the
+ * functions above; other channel counts run the first / last layer on generic CUDA-core kernels. */
+size_t f2f_dncnn_param_count_c(int channels);
+size_t f2f_dncnn_workspace_bytes_c(int B, int H, int W, int train, int channels);
+int f2f_dncnn_forward_c(const float *d_params, float *d_bn_running, long long *d_nbt,
+                        const float *d_x, float *d_y, void *d_ws, size_t ws_bytes, int B, int H,
+                        int W, int train, int residual, int channels, void *stream);
+int f2f_dncnn_backward_c(const float *d_params, float *d_grads, const float *d_dy, void *d_ws,
+                         size_t ws_bytes, int B, int H, int W, int residual, int accumulate,
+                         int channels, void *stream);
 /* torch.optim.Adam step (amsgrad = False, weight decay added to the gradient) on one flat
  * tensor; `step` counts from 1 (blind_denoising.py:163-165, 222). */
 int f2f_adam_step(float *d_p, const float *d_g, float *d_m, float *d_v, size_t n,

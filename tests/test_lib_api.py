@@ -17,8 +17,12 @@ def test_extract_config_defaults_and_errors():
         lib_api.extract_config({"net_name": "fastdvdnet"})      # outside the scope of this build
     with pytest.raises(ValueError):
         lib_api.extract_config({"net_name": "nonsense"})        # __init__.py:31,39
+    m = lib_api.load_model({"device": "cpu"})                   # the reference's default: channels = 3 (dncnn/io.py:64-67)
+    sd = m.state_dict()
+    assert tuple(sd["dncnn.0.weight"].shape) == (64, 3, 3, 3) and tuple(sd["dncnn.47.weight"].shape) == (3, 64, 3, 3)
+    assert len(sd) == 92 and m.flat_params.numel() == 556032 + 2 * 1152
     with pytest.raises(NotImplementedError):
-        lib_api.load_model({"device": "cpu"})                   # reference default channels=3 is not built
+        lib_api.load_model({"device": "cpu", "channels": 2})   # only gray and RGB are built
 
 
 @pytest.mark.gpu

@@ -100,3 +100,40 @@ def test_precise_online_loop_meets_the_psnr_contract(cuda, precise):
         diffs.append(float(psnr(clean, den[0, 0].cpu().numpy())) - g["psnr_oracle"])
     print("precise mode, PSNR - oracle per frame (dB):", " ".join("%+.4f" % d for d in diffs))
     assert np.abs(diffs).max() <= 0.05, diffs
+
+
+@pytest.mark.parametrize("mode", ["default", "precise"])
+def test_three_channel_network(cuda, mode):
+    """channels = 3, the reference loader's default (lib/frame2frame/dncnn/io.py:64-67, net.py:13,19): forward (train and
+    eval), gradients and running statistics against the stock-torch FP32 network with the same seeded weights, in both
+    modes.  Bars: precise 2e-5 / 2e-4 like the gray network; default mode 3e-2 / 6e-2 (16-bit operands)."""
+    from frame2frame_b200 import dncnn, synth
+    from oracle import dncnn_oracle as do
+    sd = synth.dncnn_state_dict(seed=3, channels=3)
+    ref = do.load_numpy_state(do.OracleDnCNN(channels=3, residual=True), sd)
+    net = torch.nn.DataParallel(dncnn.DnCNN(channels=3, residual=True), device_ids=[0]).cuda()
+    net.load_state_dict({k: torch.from_numpy(v) for k, v in sd.items()})
+    B, H, W = 2, 37, 53
+    rng = np.random.default_rng(5)
+    x = torch.from_numpy(rng.uniform(0, 1, (B, 3, H, W)).astype(np.float32))
+    dy = torch.from_numpy(rng.standard_normal((B, 3, H, W)).astype(np.float32))
+    ty, tg = (2e-5, 2e-4) if mode == "precise" else (3e-2, 6e-2)
+    dncnn.set_precise(mode == "precise")
+    try:
+        net.eval(); ref.eval()
+        with torch.no_grad():
+            assert _rel(net(x.to(cuda)), ref(x)) <= ty
+        net.train(); ref.train()
+        y, yr = net(x.to(cuda)), ref(x)
+        assert _rel(y, yr) <= ty
+        (y * dy.to(cuda)).sum().backward()
+        (yr * dy).sum().backward()
+        m = net.module
+        g, gr = m.flat_grads, do.flat_grads(ref)
+        assert g.numel() == 556032 + 2304
+        assert _rel(g, gr) <= tg
+        assert _rel(g[:1728], gr[:1728]) <= tg and _rel(g[-1728:], gr[-1728:]) <= tg      # conv0 / conv16 on their own
+        with pytest.raises(ValueError):
+            net(torch.zeros(1, 1, 8, 8, device=cuda))
+    finally:
+        dncnn.set_precise(False)
