@@ -252,6 +252,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-tvl1", action="store_true", help="f2f workload: skip the secondary TV-L1 measurement")
     ap.add_argument("--no-batch", action="store_true", help="f2f workload: skip the secondary batch-mode (NCCL) measurement")
+    ap.add_argument("--no-precise", action="store_true", help="f2f workload: skip the secondary precise-mode measurement")
     ap.add_argument("--no-config0", action="store_true", help="reference arm: skip the non-extrapolated configs[0] point")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))

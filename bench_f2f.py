@@ -360,6 +360,38 @@ def ours(args, rank, world, local_rank, ClockSampler, peaks):
         line["config0"] = {"workload": "configs[0]: %d frames 960x540, analytic flows, iter=20, from/to pinned host frames" % C0_FRAMES,
                            "value": fps, "unit": "frames/s", "psnr_delta_db": d,
                            "note": "the reference arm times the same frames on the host cores without extrapolation (its `config0`)"}
+    # ---- the contract-grade mode: FP32-class split operands on the tensor cores (f2f_dncnn_set_precise(2)) ----
+    if not getattr(args, "no_precise", False) and lib.f2f_dncnn_storage_dtype():
+        from frame2frame_b200 import dncnn
+        dncnn.set_precise(2)
+        try:
+            peng = OnlineF2F(load_network(gold, dev))
+            psteps2 = 3
+
+            def prun(k0, nsteps):
+                fr = [devf[(k0 + j) % nf] for j in range(nsteps + 1)]
+                for _ in peng.run_sequence(fr, ITERS, lookahead=LOOKAHEAD, flow_kw=FLOW_KW):
+                    pass
+            prun(0, 1)
+            torch.cuda.synchronize()
+            q0, q1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            q0.record()
+            prun(1, psteps2)
+            q1.record()
+            torch.cuda.synchronize()
+            pfps = psteps2 / (q0.elapsed_time(q1) * 1e-3)
+            blk = {"mode": "precise 2: every 64->64 operand as an FP16 hi + lo pair (22 bits), three tcgen05 products per term, "
+                           "FP32 activations / gradients between layers (csrc/dncnn_precise2.cuh)",
+                   "value": pfps, "unit": "frames/s", "steps": psteps2, "n_gpus": 1,
+                   "model_tflops_fp32_equivalent": frame_flop * pfps / 1e12,
+                   "note": "same workload as `value` (device-resident frames, flows inside), one GPU"}
+            del peng
+            if g1080 is not None:
+                d, _ = parity_leg(torch, dev, g1080, 2)
+                blk["psnr_delta_db"] = {"vs": "tests/golden/f2f_1080p_ref.json", "per_frame": d, "max_abs": float(np.max(np.abs(d)))}
+            line["precise"] = blk
+        finally:
+            dncnn.set_precise(0)
     if world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline()
     return line

@@ -199,7 +199,7 @@ def blind_denoising(**args):
     torch.cuda.set_device(dev)
     if args.get("precise"):
         from .dncnn import set_precise
-        set_precise(True)
+        set_precise(int(args["precise"]))
     model_fn = args["network"]
     if not os.path.isabs(model_fn):
         model_fn = os.path.join(os.path.abspath(os.path.dirname(__file__)), model_fn)
@@ -221,7 +221,7 @@ def blind_denoising(**args):
         """blind_denoising.py:233-253 for frame i, on the writer thread: save, score, log -- in frame order."""
         ready.synchronize()
         print(i)
-        den_np = np.array(den_host)
+        den_np = den_host.numpy()
         if _is_tiff(args["ref"]):
             imsave(args["output"] % (i), np.squeeze(255. * den_np).astype(np.float32))
         else:
@@ -312,9 +312,10 @@ def main(argv=None):
     parser.add_argument("--network", type=str, default="dncnn/logs/DnCNN-S-25/net.pth", help="path to the network")
     parser.add_argument("--gpu", type=int, default=0, help="(added) CUDA device index")
     parser.add_argument("--align_corners", action="store_true", help="(added) sample with align_corners=True")
-    parser.add_argument("--precise", action="store_true",
-                        help="(added) FP32 arithmetic throughout the network (the reference's precision; ~25x slower than the "
-                             "default 16-bit tensor-core operands)")
+    parser.add_argument("--precise", type=int, nargs="?", const=2, default=0, choices=[0, 1, 2],
+                        help="(added) FP32-class arithmetic throughout the network, the reference's precision: 2 = split FP16 "
+                             "operand pairs on the tensor cores (~5x the default mode's time), 1 = FP32 on the CUDA cores (~40x); "
+                             "default 0 = 16-bit tensor-core operands")
     parser.add_argument("--lookahead", type=int, default=16, help="(added) frame pairs per batched TV-L1 call when --flow is empty")
     # (added) TV-L1 parameters of the on-device flow used when --flow is empty; defaults = tvl1flow/tvl1flow.sh:11-18
     for name, typ in (("tau", float), ("lam", float), ("theta", float), ("nscales", int), ("fscale", int), ("zfactor", float),

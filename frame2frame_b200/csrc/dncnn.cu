@@ -62,7 +62,7 @@ using namespace tc05;
 typedef tc05::h16 h16;
 
 enum Prologue { PRO_RAW = 0, PRO_BN_RELU = 1 };
-enum Epilogue { EPI_STORE = 0, EPI_STATS = 1, EPI_DGRAD_BN = 2, EPI_DGRAD_RELU = 3 };
+enum Epilogue { EPI_STORE = 0, EPI_STATS = 1, EPI_DGRAD_BN = 2, EPI_DGRAD_RELU = 3, EPI_F32 = 4 };
 
 struct ConvArgs {
     const h16 *in;        // [H][W][64]
@@ -77,6 +77,9 @@ struct ConvArgs {
     const float *p_mean;
     const float *p_invstd;
     int H, W, tiles_x, tiles_y;
+    float *out32;          // EPI_F32: FP32 accumulators go to [H][W][64] floats: out32 = (oacc ? out32 : 0) + oscale * acc
+    float oscale;
+    int oacc;
     unsigned long long *trace;   // f2f_dncnn_set_trace: per-role cycle counters (development aid) or NULL
     int pdl_trigger;             // release the dependent launch early (f2f_common.cuh)
 };
@@ -119,6 +122,7 @@ using dn::EPI_STORE;
 using dn::EPI_STATS;
 using dn::EPI_DGRAD_BN;
 using dn::EPI_DGRAD_RELU;
+using dn::EPI_F32;
 typedef tc05::h16 h16;
 
 constexpr int TW = 8, TH = 16;
@@ -155,6 +159,33 @@ __device__ __forceinline__ void epilogue_tile(const ConvArgs &a, uint32_t tmem_a
                                               float (&acc0)[8], float (&acc1)[8], const EpiCoef &cf)
 {
     const int chunk = lane & 7;
+    if (EPI == EPI_F32) {
+        // split-operand ("precise 2") passes: the FP32 accumulators themselves are the result.  Accumulator row
+        // m = 32 wq + lane is pixel (row m / 8, column m % 8) of the tile; a lane owns its pixel's 64 floats.
+        const int m = wq * 32 + lane;
+        const int gy = ty + (m >> 3), gx = tx + (m & 7);
+        const bool inb = gy < a.H && gx < a.W;
+        float4 *dst = reinterpret_cast<float4 *>(a.out32 + ((size_t)gy * a.W + gx) * 64);
+#pragma unroll
+        for (int part = 0; part < 2; part++) {
+            uint32_t r[32];
+            tmem_ld32(tmem_addr + part * 32, r);
+            tmem_ld_wait();
+            if (inb) {
+#pragma unroll
+                for (int q = 0; q < 8; q++) {
+                    float4 v = make_float4(a.oscale * __uint_as_float(r[4 * q]), a.oscale * __uint_as_float(r[4 * q + 1]),
+                                           a.oscale * __uint_as_float(r[4 * q + 2]), a.oscale * __uint_as_float(r[4 * q + 3]));
+                    if (a.oacc) {
+                        const float4 o = dst[part * 8 + q];
+                        v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
+                    }
+                    dst[part * 8 + q] = v;
+                }
+            }
+        }
+        return;
+    }
     uint8_t *myrow = stg + lane * EPI_ROW;
 #pragma unroll
     for (int part = 0; part < 2; part++) {
@@ -578,6 +609,16 @@ static int launch_conv64t(ConvArgs a, cudaStream_t st)
     return F2F_OK;
 }
 }  // namespace dnt
+
+// 3x3 64->64 convolution of a 16-bit image with 16-bit weights whose FP32 accumulators are stored (or added, scaled) to
+// an FP32 NHWC image: one term of the split-operand products of dncnn_net.cu's tensor-core precise mode
+int conv64_f32(const void *d_in, const void *d_wprep, float *d_out32, float scale, int accumulate, int H, int W, cudaStream_t st)
+{
+    dn::ConvArgs a = {};
+    a.in = (const tc05::h16 *)d_in; a.wprep = (const tc05::h16 *)d_wprep; a.out32 = d_out32; a.oscale = scale; a.oacc = accumulate;
+    a.H = H; a.W = W;
+    return dnt::launch_conv64t<dn::PRO_RAW, dn::EPI_F32>(a, st);
+}
 
 namespace dn {
 

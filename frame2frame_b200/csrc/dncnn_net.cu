@@ -1014,7 +1014,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a)
 // dW[oc][ic][ky][kx] (+)= sum over CTA partials.  tap (ky,kx): ky < 2 -> accumulator kx, rows
 // ky*64 + ic; ky == 2 -> accumulator 3 + kx, rows ic.
 __global__ void k_wgrad_reduce(const float *__restrict__ partial, int nparts, float *__restrict__ dw, int accumulate, int trig,
-                               const unsigned *__restrict__ absmax)
+                               const unsigned *__restrict__ absmax, float extra)
 {
     if (trig) pdl_launch_dependents();
     pdl_wait();
@@ -1027,7 +1027,7 @@ __global__ void k_wgrad_reduce(const float *__restrict__ partial, int nparts, fl
     float t = 0.0f;
     for (int c = 0; c < nparts; c++) t += src[(size_t)c * PARTIAL];
     float *d = dw + ((size_t)oc * 64 + ic) * 9 + tap;
-    *d = (accumulate ? *d : 0.0f) + t * grad_unscale(absmax);
+    *d = (accumulate ? *d : 0.0f) + t * (grad_unscale(absmax) * extra);
 }
 }  // namespace wg
 
@@ -1068,10 +1068,42 @@ static int simt_blocks() { return num_sms() * 4; }
 
 static void *g_debug_dump = nullptr;   // see f2f_dncnn_set_debug_dump
 
-// 0: the default mode (16-bit tensor-core operands), 1: the FP32 mode of dncnn_precise.cuh (f2f_dncnn_set_precise)
+// 0: the default mode (16-bit tensor-core operands); 1: FP32 on the CUDA cores (dncnn_precise.cuh); 2: FP32-class
+// split operands on the tensor cores (dncnn_precise2.cuh) -- f2f_dncnn_set_precise
 static int g_precise = getenv("F2F_PRECISE") ? atoi(getenv("F2F_PRECISE")) : 0;
 
+// weight gradient of one 64->64 layer (f2f_dncnn_wgrad64) with the gradient-scale and an extra factor applied on reduction
+static int wgrad64_scaled(const void *d_act, const float *d_coef_in, void *d_g, const void *d_z, const float *d_coef,
+                          float *d_partial, float *d_dw, int H, int W, int accumulate, const unsigned *d_absmax, void *stream,
+                          float extra_scale = 1.0f)
+{
+    if (!d_act || !d_g || !d_z || !d_coef || !d_partial || !d_dw || H < 1 || W < 1) {
+        set_error("f2f_dncnn_wgrad64: bad arguments");
+        return F2F_EINVAL;
+    }
+    F2F_CUDA_CHECK((ensure_dyn_smem<wg::k_wgrad64>(wg::SMEM_BYTES)));
+    cudaStream_t st = (cudaStream_t)stream;
+    wg::Args a;
+    a.act = (const h16 *)d_act; a.coef_in = d_coef_in; a.g = (h16 *)d_g; a.z = (const h16 *)d_z; a.coef = d_coef;
+    a.partial = d_partial; a.H = H; a.W = W; a.tiles_x = cdiv(W, 16); a.tiles_y = cdiv(H, wg::TR);
+    const int ntiles = a.tiles_x * a.tiles_y;
+    const int grid = ntiles < num_sms() ? ntiles : num_sms();
+    prof_begin(1, st);
+    a.pdl_trigger = (g_pdl >> 2) & 1;
+    static const int m64 = getenv("F2F_WGRAD_M64") ? atoi(getenv("F2F_WGRAD_M64")) : 1;   // 0: M = 128 throughout (A/B, profiles/r01_m64_ab.log)
+    a.m64 = m64;
+    F2F_CUDA_CHECK(launch_pdl(1, wg::k_wgrad64, dim3(grid), dim3(wg::NTHREADS), wg::SMEM_BYTES, st, a));
+    prof_end(1, st);
+    F2F_CUDA_CHECK(launch_pdl(0, wg::k_wgrad_reduce, dim3(cdiv(9 * 4096, 256)), dim3(256), 0, st, (const float *)d_partial, grid,
+                              d_dw, accumulate, (g_pdl >> 3) & 1, d_absmax, extra_scale));
+    g_dncnn_launches += 2;
+    F2F_LAUNCH_CHECK();
+    return F2F_OK;
+}
+
+
 #include "dncnn_precise.cuh"
+#include "dncnn_precise2.cuh"
 
 }  // namespace net
 }  // namespace f2f
@@ -1084,12 +1116,17 @@ extern "C" {
 size_t f2f_dncnn_param_count(void) { return NPARAMS; }
 size_t f2f_dncnn_param_count_c(int channels) { return channels >= 1 ? NPARAMS + (size_t)2 * 576 * (channels - 1) : 0; }
 
-void f2f_dncnn_set_precise(int on) { g_precise = on != 0; }
+void f2f_dncnn_set_precise(int mode)
+{
+    g_precise = mode < 0 || mode > 2 ? 1 : mode;
+    if (g_precise == 2 && tc05::H16_FORMAT) g_precise = 1;     // the hi / lo split needs FP16's 11 bits per half (BF16 build: mode 1)
+}
 int f2f_dncnn_get_precise(void) { return g_precise; }
 
 size_t f2f_dncnn_workspace_bytes_c(int B, int H, int W, int train, int channels)
 {
     if (B < 1 || H < 1 || W < 1 || channels < 1) return 0;
+    if (g_precise == 2) return p2::make_plan2(B, H, W, train, channels).total;
     if (g_precise) return pr::make_plan_f(B, H, W, train, channels).total;
     return make_plan(B, H, W, train, channels).total;
 }
@@ -1099,6 +1136,12 @@ void f2f_dncnn_set_debug_dump(void *d_buf) { g_debug_dump = d_buf; }
 
 void f2f_dncnn_workspace_layout(int B, int H, int W, int train, size_t out[8])
 {
+    if (g_precise == 2) {
+        const p2::Plan2 p = p2::make_plan2(B, H, W, train);
+        out[0] = p.o_x; out[1] = p.o_a0; out[2] = p.o_z; out[3] = p.act32; out[4] = p.o_g0; out[5] = p.o_g1;
+        out[6] = p.o_coef; out[7] = p.o_stats_f;
+        return;
+    }
     if (g_precise) {
         const pr::PlanF p = pr::make_plan_f(B, H, W, train);
         out[0] = p.o_x; out[1] = p.o_a0; out[2] = p.o_z; out[3] = p.act_bytes; out[4] = p.o_g0; out[5] = p.o_g1;
@@ -1137,6 +1180,8 @@ static int forward_impl(const float *d_params, float *d_bn_running, long long *d
         set_error("f2f_dncnn_forward: bad arguments");
         return F2F_EINVAL;
     }
+    if (g_precise == 2)
+        return p2::forward(d_params, d_bn_running, d_nbt, d_x, d_y, d_ws, ws_bytes, B, H, W, train, residual, (cudaStream_t)stream, C);
     if (g_precise)
         return pr::forward(d_params, d_bn_running, d_nbt, d_x, d_y, d_ws, ws_bytes, B, H, W, train, residual, (cudaStream_t)stream, C);
     const Plan pl = make_plan(B, H, W, train, C);
@@ -1216,40 +1261,10 @@ static int forward_impl(const float *d_params, float *d_bn_running, long long *d
     return F2F_OK;
 }
 
-static int wgrad64_scaled(const void *d_act, const float *d_coef_in, void *d_g, const void *d_z, const float *d_coef,
-                          float *d_partial, float *d_dw, int H, int W, int accumulate, const unsigned *d_absmax, void *stream);
-
 int f2f_dncnn_wgrad64(const void *d_act, const float *d_coef_in, void *d_g, const void *d_z, const float *d_coef,
                       float *d_partial, float *d_dw, int H, int W, int accumulate, void *stream)
 {
     return wgrad64_scaled(d_act, d_coef_in, d_g, d_z, d_coef, d_partial, d_dw, H, W, accumulate, nullptr, stream);
-}
-
-static int wgrad64_scaled(const void *d_act, const float *d_coef_in, void *d_g, const void *d_z, const float *d_coef,
-                          float *d_partial, float *d_dw, int H, int W, int accumulate, const unsigned *d_absmax, void *stream)
-{
-    if (!d_act || !d_g || !d_z || !d_coef || !d_partial || !d_dw || H < 1 || W < 1) {
-        set_error("f2f_dncnn_wgrad64: bad arguments");
-        return F2F_EINVAL;
-    }
-    F2F_CUDA_CHECK((ensure_dyn_smem<wg::k_wgrad64>(wg::SMEM_BYTES)));
-    cudaStream_t st = (cudaStream_t)stream;
-    wg::Args a;
-    a.act = (const h16 *)d_act; a.coef_in = d_coef_in; a.g = (h16 *)d_g; a.z = (const h16 *)d_z; a.coef = d_coef;
-    a.partial = d_partial; a.H = H; a.W = W; a.tiles_x = cdiv(W, 16); a.tiles_y = cdiv(H, wg::TR);
-    const int ntiles = a.tiles_x * a.tiles_y;
-    const int grid = ntiles < num_sms() ? ntiles : num_sms();
-    prof_begin(1, st);
-    a.pdl_trigger = (g_pdl >> 2) & 1;
-    static const int m64 = getenv("F2F_WGRAD_M64") ? atoi(getenv("F2F_WGRAD_M64")) : 1;   // 0: M = 128 throughout (A/B, profiles/r01_m64_ab.log)
-    a.m64 = m64;
-    F2F_CUDA_CHECK(launch_pdl(1, wg::k_wgrad64, dim3(grid), dim3(wg::NTHREADS), wg::SMEM_BYTES, st, a));
-    prof_end(1, st);
-    F2F_CUDA_CHECK(launch_pdl(0, wg::k_wgrad_reduce, dim3(cdiv(9 * 4096, 256)), dim3(256), 0, st, (const float *)d_partial, grid,
-                              d_dw, accumulate, (g_pdl >> 3) & 1, d_absmax));
-    g_dncnn_launches += 2;
-    F2F_LAUNCH_CHECK();
-    return F2F_OK;
 }
 
 static int backward_impl(const float *d_params, float *d_grads, const float *d_dy, void *d_ws, size_t ws_bytes, int B, int H,
@@ -1276,6 +1291,8 @@ static int backward_impl(const float *d_params, float *d_grads, const float *d_d
         set_error("f2f_dncnn_backward: bad arguments");
         return F2F_EINVAL;
     }
+    if (g_precise == 2)
+        return p2::backward(d_params, d_grads, d_dy, d_ws, ws_bytes, B, H, W, residual, accumulate, (cudaStream_t)stream, C);
     if (g_precise)
         return pr::backward(d_params, d_grads, d_dy, d_ws, ws_bytes, B, H, W, residual, accumulate, (cudaStream_t)stream, C);
     const Plan pl = make_plan(B, H, W, 1, C);

@@ -86,6 +86,8 @@ static inline cudaError_t ensure_dyn_smem(int bytes)
     return e;
 }
 
+int conv64_f32(const void *d_in, const void *d_wprep, float *d_out32, float scale, int accumulate, int H, int W, cudaStream_t st);   // dncnn.cu
+
 static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 

@@ -30,15 +30,16 @@ def _stream():
     return torch.cuda.current_stream().cuda_stream
 
 
-def set_precise(on):
-    """Precision mode of every DnCNN in the process (f2f_dncnn_set_precise): False = the default 16-bit tensor-core
-    operands, True = the FP32 CUDA-core mode, the arithmetic of the reference's FP32 torch loop up to summation order
-    (about 25x slower).  Workspaces are re-planned on the next call."""
-    lib().f2f_dncnn_set_precise(int(bool(on)))
+def set_precise(mode):
+    """Precision mode of every DnCNN in the process (f2f_dncnn_set_precise): 0 / False = the default 16-bit tensor-core
+    operands; 1 / True = FP32 on the CUDA cores, the arithmetic of the reference's FP32 torch loop up to summation order
+    (~40x slower); 2 = FP32-class split operands (hi + lo FP16 pairs, three products) on the tensor cores (~5x slower).
+    Workspaces are re-planned on the next call."""
+    lib().f2f_dncnn_set_precise(int(mode))
 
 
 def get_precise():
-    return bool(lib().f2f_dncnn_get_precise())
+    return int(lib().f2f_dncnn_get_precise())
 
 
 class _Workspace:

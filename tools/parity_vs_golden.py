@@ -10,9 +10,10 @@ from frame2frame_b200.dncnn import DnCNN
 
 root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 argv = [a for a in sys.argv[1:] if not a.startswith("--")]
-if "--precise" in sys.argv:
-    from frame2frame_b200.dncnn import set_precise
-    set_precise(True)
+for a in sys.argv:
+    if a.startswith("--precise"):
+        from frame2frame_b200.dncnn import set_precise
+        set_precise(int(a.split("=")[1]) if "=" in a else 1)
 gold = json.load(open(argv[1] if len(argv) > 1 else os.path.join(root, "tests", "golden", "f2f_config0_ref.json")))
 W, H = (int(v) for v in gold["frame"].split("x"))
 ITERS, NF = gold["iters"], len(gold["frames"])
@@ -30,7 +31,7 @@ for t, den in eng.run_sequence(frames, ITERS, flows=flows, losses=losses):
                 "loss_first_dev": losses[(t - 1) * ITERS] / g["loss_first"][0] - 1, "loss_last_dev": losses[t * ITERS - 1] / g["loss_last"][0] - 1})
     print("t=%d  PSNR %.3f  oracle %.3f  diff %+.3f dB   loss dev first %+.1e last %+.1e" % (t, p, g["psnr_oracle"], rec[-1]["diff_db"], rec[-1]["loss_first_dev"], rec[-1]["loss_last_dev"]))
 d = [r["diff_db"] for r in rec]
-dt = "fp32 (precise)" if _lib.lib().f2f_dncnn_get_precise() else ("fp16" if _lib.lib().f2f_dncnn_storage_dtype() else "bf16")
+dt = ["", "fp32 CUDA cores (precise 1)", "split fp16 pairs on tensor cores (precise 2)"][_lib.lib().f2f_dncnn_get_precise()] if _lib.lib().f2f_dncnn_get_precise() else ("fp16" if _lib.lib().f2f_dncnn_storage_dtype() else "bf16")
 print("storage %s: mean diff %+.4f dB, max |diff| %.4f dB" % (dt, np.mean(d), np.max(np.abs(d))))
 if argv:
     json.dump({"storage": dt, "frames": rec, "mean_diff_db": float(np.mean(d)), "max_abs_diff_db": float(np.max(np.abs(d)))}, open(argv[0], "w"), indent=1)
