@@ -34,6 +34,7 @@ def _declare(lib):
     lib.f2f_tvl1_flow_bidir.argtypes = [fp, fp, fp, C.c_int, C.c_int, C.c_int, C.POINTER(Tvl1Params), ip, vp, sz, vp]
     lib.f2f_tvl1_flow_batch_host.argtypes = [fp, fp, fp, C.c_int, C.c_int, C.c_int, C.POINTER(Tvl1Params), ip, C.c_int]
     lib.f2f_tvl1_gaussian.argtypes = [fp, C.c_int, C.c_int, C.c_double, fp, vp]
+    lib.f2f_tvl1_gaussian_noalloc.argtypes = [fp, C.c_int, C.c_int, C.c_double, vp]
     lib.f2f_tvl1_zoom_out.argtypes = [fp, fp, C.c_int, C.c_int, C.c_float, fp, vp]
     lib.f2f_tvl1_zoom_in_scaled.argtypes = [fp, fp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, vp]
     lib.f2f_tvl1_centered_gradient.argtypes = [fp, fp, fp, C.c_int, C.c_int, vp]

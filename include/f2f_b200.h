@@ -129,6 +129,18 @@ void Dual_TVL1_optic_flow_multiscale(float *I0, float *I1, float *u1, float *u2,
  * be parity-tested against the reference function it replaces. */
 int f2f_tvl1_gaussian(float *d_I, int nx, int ny, double sigma, float *d_tmp,
                       void *stream);                       /* mask.c:223-339  */
+/* Allocation-free variant of f2f_tvl1_gaussian.  NO counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid allocation).  The intermediate image of the
+ * row pass lives in a file-scope `static __device__` array of F2F_NOALLOC_MAX_PIXELS floats
+ * (8.3 MB, held by every GPU that loads the library until exit); the call allocates nothing and
+ * calls no allocating library routine.  nx * ny > F2F_NOALLOC_MAX_PIXELS returns F2F_EINVAL.
+ * Every call on a device shares the array: calls that overlap on the GPU (two streams, two host
+ * threads) RACE on it -- serialise them on one stream.  Nothing in the array must start at zero
+ * (the row pass writes every element the column pass reads), so it is not cleared between calls.
+ * Result: bit-identical to f2f_tvl1_gaussian. */
+#define F2F_NOALLOC_MAX_PIXELS (1920 * 1080)
+int f2f_tvl1_gaussian_noalloc(float *d_I, int nx, int ny, double sigma, void *stream);
 int f2f_tvl1_zoom_out(const float *d_I, float *d_out, int nx, int ny, float factor,
                       float *d_tmp2, void *stream);        /* zoom.c:43-81 (d_tmp2: 2*nx*ny) */
 int f2f_tvl1_zoom_in_scaled(const float *d_I, float *d_out, int nx, int ny, int nxx,
@@ -244,8 +256,11 @@ void f2f_dncnn_set_trace(unsigned long long *d_counters);
  *   1 ("precise"): everything in FP32 on the CUDA cores (csrc/dncnn_precise.cuh) -- the arithmetic of the reference's
  *      FP32 torch path (blind_denoising.py:211-230) up to summation order, ~25x slower; the setting in which the
  *      online loop is held to north_star's 0.05 dB PSNR tolerance independently of 16-bit rounding.
+ *   2 ("split operand"): every FP32 operand as an FP16 hi + lo/2048 pair, three tcgen05 products per GEMM, FP32
+ *      activations between layers (csrc/dncnn_precise2.cuh): FP32-class arithmetic on the tensor cores, ~5x slower
+ *      than mode 0.  FP16 builds only; a BF16 build falls back to mode 1.
  * F2F_PRECISE in the environment sets the initial value.  Process-global, like the other switches. */
-void f2f_dncnn_set_precise(int on);
+void f2f_dncnn_set_precise(int mode);
 int f2f_dncnn_get_precise(void);
 /* Programmatic dependent launch of the per-layer DnCNN kernel chain: bit mask, default 3 (launch attribute on the big
  * and the small kernels, no early trigger); 0 launches the same kernels fully serialised (F2F_PDL in the environment
