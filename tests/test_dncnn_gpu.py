@@ -247,18 +247,24 @@ def test_run_sequence_equals_frame_by_frame(cuda):
 def test_blind_denoising_cli(cuda, tmp_path):
     """The reference's command line (blind_denoising.py:262-298) on PNG frames: denoised PNGs, one PSNR per
     line, [model, optimizer] checkpoint; with --flow files (.flo, readFlowFile.py layout) and without (TV-L1 on
-    the device) the outputs exist and the PSNRs agree to within the flow difference."""
+    the device) the outputs exist; the .flo files hold the TV-L1 flows of the same frames (what tvl1flow.sh would
+    have written), so both routes see the same flows and their PSNRs agree.  (Analytic flows in the files are no
+    yardstick here: on 64x96 frames at sigma = 25 the estimated flow differs from the true one by enough to move a
+    2-iteration fine-tune by 1-2 dB.)"""
     from PIL import Image
     from frame2frame_b200 import blind_denoising as bd, synth
-    from frame2frame_b200.tvl1 import write_flo
+    from frame2frame_b200.tvl1 import tvl1flow, write_flo
+    from frame2frame_b200.tvl1flow_cli import SCRIPT_PARAMS
     H, W, NF = 64, 96, 3
+    kw = dict(SCRIPT_PARAMS, fscale=0, nscales=3)
+    up = lambda t: torch.from_numpy(synth.noisy_frame(H, W, t).astype(np.uint8).astype(np.float32) / np.float32(255.0)).to(cuda) * 255.0
     sd = {k: torch.from_numpy(v) for k, v in synth.pretrained_state_dict().items()}
     torch.save(sd, str(tmp_path / "net.pth"))
     for t in range(NF + 1):
         Image.fromarray(synth.noisy_frame(H, W, t).astype(np.uint8)).save(str(tmp_path / ("in_%03d.png" % t)))
         Image.fromarray(synth.clean_frame_u8(H, W, t).astype(np.uint8)).save(str(tmp_path / ("ref_%03d.png" % t)))
         if t:
-            write_flo(str(tmp_path / ("flow_%03d.flo" % t)), synth.backward_flow(H, W, t))
+            write_flo(str(tmp_path / ("flow_%03d.flo" % t)), tvl1flow(up(t), up(t - 1), **kw).cpu().numpy())
     common = ["--input", str(tmp_path / "in_%03d.png"), "--ref", str(tmp_path / "ref_%03d.png"), "--first", "0",
               "--last", str(NF), "--iter", "2", "--network", str(tmp_path / "net.pth")]
     res = {}
@@ -274,7 +280,7 @@ def test_blind_denoising_cli(cuda, tmp_path):
             assert im.shape == (H, W) and im.dtype == np.uint8
         model, opt = torch.load(str(out / "final.pth"), weights_only=False)
         assert any(k.startswith("module.dncnn.0.") for k in model.state_dict())
-    assert np.allclose(res["files"], res["tvl1"], atol=1.0)
+    assert np.allclose(res["files"], res["tvl1"], atol=0.02), res
 
 
 def test_cli_on_second_gpu_equals_first(cuda, tmp_path):
