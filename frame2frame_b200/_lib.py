@@ -58,6 +58,8 @@ def _declare(lib):
     lib.f2f_dncnn_set_trace.restype = None
     lib.f2f_set_pdl.argtypes = [C.c_int]
     lib.f2f_set_pdl.restype = None
+    lib.f2f_set_serpentine.argtypes = [C.c_int]
+    lib.f2f_set_serpentine.restype = None
     lib.f2f_set_conv_pair.argtypes = [C.c_int]
     lib.f2f_set_conv_pair.restype = None
     lib.f2f_dncnn_storage_dtype.restype = C.c_int

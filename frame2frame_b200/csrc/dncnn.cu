@@ -55,6 +55,7 @@ void prof_end(int cls, cudaStream_t st)
 
 int g_conv_pair = getenv("F2F_CONV_PAIR") ? atoi(getenv("F2F_CONV_PAIR")) : 0;   // CTA-pair (cta_group::2) convolutions, experimental
 int g_pdl = getenv("F2F_PDL") ? atoi(getenv("F2F_PDL")) : 3;   // programmatic dependent launch, see f2f_common.cuh
+int g_serpentine = getenv("F2F_SERPENTINE") ? atoi(getenv("F2F_SERPENTINE")) : 1, g_tile_rev = 0;   // f2f_common.cuh
 
 namespace dn {
 
@@ -82,6 +83,7 @@ struct ConvArgs {
     int oacc;
     unsigned long long *trace;   // f2f_dncnn_set_trace: per-role cycle counters (development aid) or NULL
     int pdl_trigger;             // release the dependent launch early (f2f_common.cuh)
+    int rev;                     // tile order: 0 = top-down, 1 = bottom-up (L2 reuse between consecutive launches)
 };
 
 unsigned long long *g_conv_trace = nullptr;
@@ -275,6 +277,10 @@ k_conv64t(ConvArgs a, const __grid_constant__ CUtensorMap tm_in, const __grid_co
     const bool leader = rank == 0;
     const int first_tile = PAIR ? (int)(blockIdx.x & ~1u) : (int)blockIdx.x;
     const int nit = first_tile < ntiles ? (ntiles - first_tile + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+    // a.rev: walk the image bottom-up.  Consecutive launches of the layer chain alternate the direction, so that a
+    // launch starts on the part of its input the previous launch touched LAST -- still in the 126 MB L2 -- instead of
+    // the part evicted first (a 1080p activation is 265 MB).
+    auto tile_of = [&](int t) { return (!PAIR && a.rev) ? ntiles - 1 - t : t; };
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < NA; s++) {
@@ -305,7 +311,7 @@ k_conv64t(ConvArgs a, const __grid_constant__ CUtensorMap tm_in, const __grid_co
             const bool tr = a.trace != nullptr;
             long long tr_wait = 0;
             for (int it = 0; it < nit; it++) {
-                const int tile = blockIdx.x + it * gridDim.x;
+                const int tile = tile_of(blockIdx.x + it * gridDim.x);
                 const int s = it % NA;
                 const int ty0 = (tile / a.tiles_x) * TH - 1, tx0 = (tile % a.tiles_x) * TW - 1;
                 const long long t0 = tr ? clock64() : 0;
@@ -329,7 +335,7 @@ k_conv64t(ConvArgs a, const __grid_constant__ CUtensorMap tm_in, const __grid_co
         if (DGRAD && elect_one()) {
             tma_prefetch_desc(&tm_z);
             for (int it = 0; it < nit; it++) {
-                const int tile = blockIdx.x + it * gridDim.x;
+                const int tile = tile_of(blockIdx.x + it * gridDim.x);
                 const int s = it % NZ;
                 const int ty0 = (tile / a.tiles_x) * TH, tx0 = (tile % a.tiles_x) * TW;
                 mbar_wait(BAR(B_EMPTY_Z + s), ((it / NZ) & 1) ^ 1);
@@ -346,7 +352,7 @@ k_conv64t(ConvArgs a, const __grid_constant__ CUtensorMap tm_in, const __grid_co
 #pragma unroll
         for (int j = 0; j < 8; j++) { sc[j] = a.scale[chunk * 8 + j]; sh[j] = a.shift[chunk * 8 + j]; }
         for (int it = 0; it < nit; it++) {
-            const int tile = blockIdx.x + it * gridDim.x;
+            const int tile = tile_of(blockIdx.x + it * gridDim.x);
             const int s = it % NA;
             const int ty0 = (tile / a.tiles_x) * TH - 1, tx0 = (tile % a.tiles_x) * TW - 1;
             uint8_t *st = smem + OFF_A + s * A_STAGE;
@@ -487,7 +493,7 @@ k_conv64t(ConvArgs a, const __grid_constant__ CUtensorMap tm_in, const __grid_co
         const long long tr_start = tr ? clock64() : 0;
         int ntr = 0;
         for (int it = set; it < nit; it += 2) {
-            const int tile = blockIdx.x + it * gridDim.x;
+            const int tile = tile_of(blockIdx.x + it * gridDim.x);
             const int sz = it % NZ;
             const int ty = (tile / a.tiles_x) * TH, tx = (tile % a.tiles_x) * TW;
             const long long t0 = tr ? clock64() : 0;
@@ -599,6 +605,7 @@ static int launch_conv64t(ConvArgs a, cudaStream_t st)
     const dim3 block(PRO == dn::PRO_BN_RELU ? NTHREADS_BN : NTHREADS_RAW);
     prof_begin(0, st);
     a.pdl_trigger = (g_pdl >> 2) & 1;
+    a.rev = g_tile_rev;
     if (g_conv_pair)      // an even number of CTAs: the last pair's second CTA may only have all-zero tiles
         F2F_CUDA_CHECK(launch_pdl_pairs(1, k_conv64t<PRO, EPI, true>, dim3((grid + 1) & ~1), block, SMEM_BYTES, st, a, tm_in, tm_z));
     else
@@ -671,6 +678,7 @@ void f2f_profile_dncnn_read(double out[4])
 
 void f2f_dncnn_set_trace(unsigned long long *d_counters) { g_conv_trace = d_counters; }
 void f2f_set_pdl(int on) { f2f::g_pdl = on; }
+void f2f_set_serpentine(int on) { f2f::g_serpentine = on; f2f::g_tile_rev = 0; }
 void f2f_set_conv_pair(int on) { f2f::g_conv_pair = on; }
 int f2f_dncnn_storage_dtype(void) { return tc05::H16_FORMAT ? 0 : 1; }
 

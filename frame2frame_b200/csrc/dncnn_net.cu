@@ -807,6 +807,7 @@ struct Args {
     int H, W, tiles_x, tiles_y;
     int pdl_trigger;
     int m64;               // taps ky = 2 as M = 64 instructions (F2F_WGRAD_M64)
+    int rev;               // tile order: 1 = bottom-up (f2f_common.cuh, g_tile_rev)
 };
 
 __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a)
@@ -857,7 +858,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a)
             const int s = it % STAGES;
             mbar_wait(BAR(STAGES + s), ((it / STAGES) & 1) ^ 1);
             uint8_t *dstA = smem + s * STAGE;
-            const int ty0 = (tile / a.tiles_x) * TR - 1, tx0 = (tile % a.tiles_x) * 16 - 1;
+            const int tpos = a.rev ? ntiles - 1 - tile : tile;
+            const int ty0 = (tpos / a.tiles_x) * TR - 1, tx0 = (tpos % a.tiles_x) * 16 - 1;
             constexpr int U = (HPIX + 15) / 16;   // the whole tile's loads in flight at once
             uint4 v[U];
             uint32_t inb = 0;
@@ -931,7 +933,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a)
             const int s = it % STAGES;
             mbar_wait(BAR(STAGES + s), ((it / STAGES) & 1) ^ 1);
             uint8_t *dstD = smem + s * STAGE + A_BYTES;
-            const int ty0 = (tile / a.tiles_x) * TR, tx0 = (tile % a.tiles_x) * 16;
+            const int tpos = a.rev ? ntiles - 1 - tile : tile;
+            const int ty0 = (tpos / a.tiles_x) * TR, tx0 = (tpos % a.tiles_x) * 16;
             constexpr int U = DPIX / 32;          // two passes of 4 rounds x 16 pixels (register budget: 17 warps -> 96 registers)
 #pragma unroll 1
             for (int r0 = 0; r0 < DPIX / 16; r0 += U) {
@@ -1092,6 +1095,7 @@ static int wgrad64_scaled(const void *d_act, const float *d_coef_in, void *d_g, 
     a.pdl_trigger = (g_pdl >> 2) & 1;
     static const int m64 = getenv("F2F_WGRAD_M64") ? atoi(getenv("F2F_WGRAD_M64")) : 1;   // 0: M = 128 throughout (A/B, profiles/r01_m64_ab.log)
     a.m64 = m64;
+    a.rev = g_tile_rev;
     F2F_CUDA_CHECK(launch_pdl(1, wg::k_wgrad64, dim3(grid), dim3(wg::NTHREADS), wg::SMEM_BYTES, st, a));
     prof_end(1, st);
     F2F_CUDA_CHECK(launch_pdl(0, wg::k_wgrad_reduce, dim3(cdiv(9 * 4096, 256)), dim3(256), 0, st, (const float *)d_partial, grid,
@@ -1225,9 +1229,11 @@ static int forward_impl(const float *d_params, float *d_bn_running, long long *d
         const h16 *in = k == 1 ? a0 : zbuf(k - 1);
         const float *cf = k == 1 ? nullptr : coef + (size_t)(k - 2) * C_STRIDE;
         for (int b = 0; b < B; b++) {
+            tile_dir(k & 1);      // a0 / z_{k-1} was written in the opposite direction: start where it ended (L2)
             const int rc = f2f_dncnn_conv64(in + b * P * 64, zbuf(k) + b * P * 64, wprep + (size_t)(k - 1) * WSZ,
                                             cf ? cf + C_SCALE : nullptr, cf ? cf + C_SHIFT : nullptr,
                                             train ? stats_f + (size_t)(k - 1) * 128 : nullptr, H, W, stream);
+            tile_dir(0);
             if (rc) return rc;
         }
         if (train) {
@@ -1355,9 +1361,11 @@ static int backward_impl(const float *d_params, float *d_grads, const float *d_d
         const h16 *act = k == 1 ? a0 : zbuf(k - 1);
         const float *cf_in = k == 1 ? nullptr : coef + (size_t)(k - 2) * C_STRIDE;
         for (int b = 0; b < B; b++) {
+            tile_dir(1);          // g_k was written top-down (k_last_bwd / the input gradient below): start at its end (L2)
             int rc = wgrad64_scaled(act + b * P * 64, cf_in, gbuf[cur] + b * P * 64, zbuf(k) + b * P * 64, cf, partial,
                                     d_grads + off_conv(k), H, W, accumulate || b > 0, absmax, stream);
             if (rc) return rc;
+            tile_dir(0);          // ... and the input gradient reads dz_k from where the weight gradient finished it
             if (b == B - 1) dump(2 * (k - 1) + 1, gbuf[cur]);
             // input gradient: g_{k-1} = relu'/BN-sums( conv(dz_k, W_k^T) )
             if (k >= 2)

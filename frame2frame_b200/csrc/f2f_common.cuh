@@ -38,6 +38,12 @@ void prof_end(int cls, cudaStream_t st);
 // the dependents early from a persistent kernel that owns every SM only parks their CTAs, so it is off.
 extern int g_conv_pair;   // 1: the 64->64 convolutions run as CTA pairs (cta_group::2), F2F_CONV_PAIR / f2f_set_conv_pair
 extern int g_pdl;   // bit 0: attribute on the big kernels, 1: on the small ones, 2: early trigger in the big, 3: in the small
+// Tile order of the NEXT 64->64 launch (conv, input gradient, weight gradient): 0 = top-down, 1 = bottom-up.  The
+// layer-chain drivers alternate it so that every launch begins on the rows its predecessor touched last, which are
+// still in L2 (f2f_set_serpentine / F2F_SERPENTINE: 0 leaves every launch top-down).  Results do not depend on it
+// beyond FP32 summation order of the per-CTA weight-gradient partials and of the BatchNorm sums.
+extern int g_serpentine, g_tile_rev;
+inline void tile_dir(int rev) { g_tile_rev = g_serpentine ? rev : 0; }
 template <class... KArgs, class... Args>
 static inline cudaError_t launch_pdl(int big, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args)
 {

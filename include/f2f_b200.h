@@ -266,6 +266,12 @@ int f2f_dncnn_get_precise(void);
  * and the small kernels, no early trigger); 0 launches the same kernels fully serialised (F2F_PDL in the environment
  * sets the initial value).  Results are identical, only the gaps between kernels differ (csrc/f2f_common.cuh). */
 void f2f_set_pdl(int on);
+/* Serpentine tile order of the 64->64 layer chain (default 1, F2F_SERPENTINE in the environment): consecutive launches
+ * walk the image in opposite directions (forward: odd layers bottom-up; backward: weight gradient bottom-up, input
+ * gradient top-down), so every launch starts on the rows its predecessor touched last, which the 126 MB L2 still
+ * holds -- a 1080p activation is 265 MB.  0 = every launch top-down.  Same results up to FP32 summation order of
+ * the weight-gradient partials and BatchNorm sums. */
+void f2f_set_serpentine(int on);
 /* Experimental: on != 0 runs the 64->64 convolutions (forward and input gradient) as CTA pairs -- clusters of two
  * CTAs issuing one tcgen05.mma.cta_group::2 M = 256 instruction stream, each CTA supplying half of the weights
  * (F2F_CONV_PAIR in the environment sets the initial value, default 0).  Same results bit for bit. */
