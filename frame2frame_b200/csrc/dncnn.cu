@@ -377,8 +377,7 @@ k_conv64t(ConvArgs a, const __grid_constant__ CUtensorMap tm_in, const __grid_co
 #pragma unroll
                     for (int j = 0; j < 4; j++) {
                         const float2 f = unpack_h16(w[j]);
-                        w[j] = pack_h16(fmaxf(fmaf(f.x, sc[2 * j], sh[2 * j]), 0.0f),
-                                         fmaxf(fmaf(f.y, sc[2 * j + 1], sh[2 * j + 1]), 0.0f));
+                        w[j] = pack_h16_relu(fmaf(f.x, sc[2 * j], sh[2 * j]), fmaf(f.y, sc[2 * j + 1], sh[2 * j + 1]));
                     }
                     *reinterpret_cast<uint4 *>(st + pix * 128 + ((chunk ^ (pix & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
                 }

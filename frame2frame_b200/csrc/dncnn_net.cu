@@ -376,7 +376,7 @@ __global__ void __launch_bounds__(FT) k_first_fwd(const float *__restrict__ x, c
                 const float xv = x0[x_ + (t / 3) * XW + (t % 3)];
                 s0 = fmaf(xv, w[t][0], s0); s1 = fmaf(xv, w[t][1], s1);
             }
-            *reinterpret_cast<uint32_t *>(orow + (size_t)x_ * 64) = pack_h16(fmaxf(s0, 0.0f), fmaxf(s1, 0.0f));
+            *reinterpret_cast<uint32_t *>(orow + (size_t)x_ * 64) = pack_h16_relu(s0, s1);
         }
     }
 }
@@ -883,8 +883,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a)
 #pragma unroll
                         for (int j = 0; j < 4; j++) {
                             const float2 f = unpack_h16(w[j]);
-                            w[j] = pack_h16(fmaxf(fmaf(f.x, sc[2 * j], sh[2 * j]), 0.0f),
-                                             fmaxf(fmaf(f.y, sc[2 * j + 1], sh[2 * j + 1]), 0.0f));
+                            w[j] = pack_h16_relu(fmaf(f.x, sc[2 * j], sh[2 * j]), fmaf(f.y, sc[2 * j + 1], sh[2 * j + 1]));
                         }
                         o = make_uint4(w[0], w[1], w[2], w[3]);
                     }

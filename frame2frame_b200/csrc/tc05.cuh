@@ -281,6 +281,14 @@ __device__ __forceinline__ float2 unpack_h16(uint32_t v)
     return __half22float2(*reinterpret_cast<const __half2 *>(&v));
 }
 __device__ __forceinline__ h16 float_to_h16(float v) { return __float2half_rn(v); }
+// pack_h16(max(lo, 0), max(hi, 0)) as ONE conversion (cvt.rn.relu: negative inputs give +0; rounding is monotone, so
+// relu-then-round and round-then-relu agree bit for bit)
+__device__ __forceinline__ uint32_t pack_h16_relu(float lo, float hi)
+{
+    uint32_t r;
+    asm("cvt.rn.relu.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    return r;
+}
 #else
 __device__ __forceinline__ uint32_t pack_h16(float lo, float hi)
 {
@@ -292,6 +300,12 @@ __device__ __forceinline__ float2 unpack_h16(uint32_t v)
     return make_float2(__uint_as_float(v << 16), __uint_as_float(v & 0xffff0000u));
 }
 __device__ __forceinline__ h16 float_to_h16(float v) { return __float2bfloat16(v); }
+__device__ __forceinline__ uint32_t pack_h16_relu(float lo, float hi)
+{
+    uint32_t r;
+    asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    return r;
+}
 #endif
 
 }  // namespace tc05

@@ -8,6 +8,8 @@
 //           starting at any 128-B row; B SWIZZLE_128B K-major
 //   mode 3  as 2 but every view 1024-B aligned, SBO 1024 (plain GEMM): reference rate
 //   mode 4  as 2 with descriptor base_offset = (start >> 7) & 7
+//   ts      A operand FROM TENSOR MEMORY (tcgen05.mma [d], [a_tmem], b_desc, ...), staged with tcgen05.st (check) /
+//           tcgen05.cp (rate): k_ts below
 // build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o ubench_mma tools/ubench_mma.cu
 #include <cstdio>
 #include <cstdlib>
@@ -16,7 +18,7 @@
 #include "../frame2frame_b200/csrc/tc05.cuh"
 
 using namespace tc05;
-typedef __nv_bfloat16 bf16;
+typedef h16 bf16;   // the library's 16-bit operand type (FP16 by default, BF16 with -DF2F_STORE_BF16): idesc_h16 follows it
 
 constexpr int HWD = 18, HPIX = 324;
 constexpr int CH_STRIDE = (HPIX + 1) * 16;
@@ -45,13 +47,13 @@ __global__ void __launch_bounds__(128, 1) k_bench(int mode, int reps, float *out
         const int p = i / 64, c = i % 64;
         const size_t off = sw ? (size_t)p * 128 + (((c >> 3) ^ (p & 7)) << 4) + (c & 7) * 2
                               : (size_t)(c >> 3) * CH_STRIDE + (size_t)p * 16 + (c & 7) * 2;
-        *(bf16 *)(A + off) = __float2bfloat16((float)aval(p, c));
+        *(bf16 *)(A + off) = float_to_h16((float)aval(p, c));
     }
     for (int i = threadIdx.x; i < 9 * 64 * 64; i += blockDim.x) {
         const int t = i / 4096, n = (i / 64) % 64, k = i % 64;
         const size_t off = sw ? (size_t)t * B_TAP + n * 128 + (((k >> 3) ^ (n & 7)) << 4) + (k & 7) * 2
                               : (size_t)t * B_TAP + (k >> 3) * 1024 + n * 16 + (k & 7) * 2;
-        *(bf16 *)(B + off) = __float2bfloat16((float)bval(t, n, k));
+        *(bf16 *)(B + off) = float_to_h16((float)bval(t, n, k));
     }
     if (threadIdx.x == 0) { mbar_init(smem_u32(bar), 1); mbar_fence_init(); }
     if (threadIdx.x < 32) tmem_alloc(smem_u32(tmem_ptr), 512);
@@ -116,6 +118,7 @@ __global__ void __launch_bounds__(128, 1) k_bench(int mode, int reps, float *out
 }
 
 void issue_variants(long long *d_cyc);
+void ts_variants(float *d_out, long long *d_cyc);
 
 int main()
 {
@@ -181,6 +184,7 @@ int main()
         avg /= 148;
         printf("mode 3, N = %3d: %.1f cycles per MMA (floor %d)\n", N, avg / (reps * 72), N / 2);
     }
+    ts_variants(d_out, d_cyc);
     return 0;
 }
 
@@ -256,4 +260,176 @@ void issue_variants(long long *d_cyc)
 {
     run_issue<0>(d_cyc);
     run_issue<1>(d_cyc);
+}
+
+// ---------------------------------------------------------------------------------------------
+// A FROM TENSOR MEMORY (".ts" form): tcgen05.mma [d_tmem], [a_tmem], b_desc, idesc.  The A tile (M = 128 rows =
+// lanes, K along the columns, two 16-bit elements per 32-bit column) is read from TMEM, so an instruction reads only
+// the 2 KB B operand from shared memory instead of 4 + 2 KB.  Views of A that differ by a K offset are column offsets
+// (that is the weight gradient's case: K = pixels, taps = pixel shifts); views that differ by an M offset -- the
+// forward convolution's taps, M = pixels -- are NOT addressable, every tap would need its own staged copy.
+//   CP = 0: A written once with tcgen05.st (known values, result checked), 72 MMAs per repetition
+//   CP = n: additionally n tcgen05.cp.128x128b (128 rows x 16 B each, 2 KB) per repetition from shared memory,
+//           the staging traffic of a kernel that re-stages its A tile (16 = one 128 x 64 tile x 2 copies)
+__host__ __device__ inline int tsval(int m, int k) { return ((m * 5 + k * 3) % 11) - 5; }
+
+__device__ __forceinline__ void mma_ts_el(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t idesc, uint32_t accumulate, uint32_t elected)
+{
+    asm volatile(
+        "{\n\t.reg .pred p, q;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "setp.ne.b32 q, %5, 0;\n\t"
+        "@q tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(elected)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_cp_128x128b(uint32_t taddr, uint64_t sdesc, uint32_t elected)
+{
+    asm volatile(
+        "{\n\t.reg .pred q;\n\t"
+        "setp.ne.b32 q, %2, 0;\n\t"
+        "@q tcgen05.cp.cta_group::1.128x128b [%0], %1;\n\t}" ::"r"(taddr), "l"(sdesc), "r"(elected)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32])
+{
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
+        ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
+          "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]),
+          "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]),
+          "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+        : "memory");
+}
+
+template <int CP>
+__global__ void __launch_bounds__(128, 1) k_ts(int reps, float *out, long long *cycles)
+{
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint8_t *A = smem, *B = smem + A_BYTES;
+    uint64_t *bar = (uint64_t *)(smem + A_BYTES + 9 * B_TAP);
+    uint32_t *tmem_ptr = (uint32_t *)(bar + 2);
+    for (int i = threadIdx.x; i < A_BYTES / 16; i += blockDim.x) ((uint4 *)A)[i] = make_uint4(0, 0, 0, 0);
+    for (int i = threadIdx.x; i < 9 * 64 * 64; i += blockDim.x) {
+        const int t = i / 4096, n = (i / 64) % 64, k = i % 64;
+        *(bf16 *)(B + (size_t)t * B_TAP + n * 128 + (((k >> 3) ^ (n & 7)) << 4) + (k & 7) * 2) = float_to_h16((float)bval(t, n, k));
+    }
+    if (threadIdx.x == 0) { mbar_init(smem_u32(bar), 1); mbar_fence_init(); }
+    if (threadIdx.x < 32) tmem_alloc(smem_u32(tmem_ptr), 512);
+    fence_proxy_async();
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem = *tmem_ptr, tmem_a = tmem + 128, tmem_scratch = tmem + 256;
+    {   // A[m][k], k = 0..255: lane m, column k / 2, low half = even k
+        const int warp = threadIdx.x >> 5, m = threadIdx.x;
+        for (int part = 0; part < 4; part++) {
+            uint32_t r[32];
+            for (int q = 0; q < 32; q++) {
+                const int k = 2 * (part * 32 + q);
+                r[q] = pack_h16((float)tsval(m, k), (float)tsval(m, k + 1));
+            }
+            tmem_st32(tmem_a + ((uint32_t)(warp * 32) << 16) + part * 32, r);
+        }
+        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+    }
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    if (threadIdx.x < 32) {
+        const uint32_t el = elect_one();
+        constexpr uint32_t IDESC = idesc_h16(128, 64, 0, 0);
+        const uint64_t b0 = desc_sw128(smem_u32(B), 1024, 0);
+        const uint32_t b_lo = (uint32_t)b0, b_hi = (uint32_t)(b0 >> 32);
+        const uint64_t c0 = smem_desc(smem_u32(A), 128, 128);     // 128 rows x 16 B: 8-row core matrices 128 B apart
+        const uint32_t c_lo = (uint32_t)c0, c_hi = (uint32_t)(c0 >> 32);
+        const long long t0 = clock64();
+        for (int rep = 0; rep < reps; rep++) {
+#pragma unroll
+            for (int c = 0; c < CP; c++)
+                tmem_cp_128x128b(tmem_scratch + (c & 15) * 4, ((uint64_t)c_hi << 32) | (c_lo + (c & 15) * 128), el);
+#pragma unroll
+            for (int tap = 0; tap < 9; tap++) {
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const uint64_t bd = ((uint64_t)b_hi << 32) | (b_lo + tap * (B_TAP / 16) + j * 2);
+#pragma unroll
+                    for (int h = 0; h < 2; h++)
+                        mma_ts_el(tmem + h * 64, tmem_a + tap * 8 + j * 8, bd, IDESC, (rep | tap | j) != 0, el);
+                }
+            }
+        }
+        if (el) mma_commit(smem_u32(bar));
+        __syncwarp();
+        mbar_wait(smem_u32(bar), 0);
+        const long long t1 = clock64();
+        if (cycles && threadIdx.x == 0) cycles[blockIdx.x] = t1 - t0;
+    }
+    __syncthreads();
+    fence_after_sync();
+    if (out && blockIdx.x == 0) {
+        const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+        for (int part = 0; part < 4; part++) {
+            uint32_t r[32];
+            tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + part * 32, r);
+            tmem_ld_wait();
+            for (int q = 0; q < 32; q++) out[(size_t)(warp * 32 + lane) * 128 + part * 32 + q] = __uint_as_float(r[q]);
+        }
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (threadIdx.x < 32) tmem_dealloc(tmem, 512);
+}
+
+template <int CP>
+static bool run_ts(float *d_out, long long *d_cyc, bool check)
+{
+    cudaFuncSetAttribute(k_ts<CP>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
+    std::vector<long long> cyc(148);
+    long bad = -1;
+    double maxerr = 0;
+    if (check) {
+        std::vector<float> out(128 * 128);
+        cudaMemset(d_out, 0, 128 * 128 * 4);
+        k_ts<CP><<<1, 128, SMEM>>>(1, d_out, nullptr);
+        cudaError_t e = cudaDeviceSynchronize();
+        if (e != cudaSuccess) { printf("ts (cp %d): %s\n", CP, cudaGetErrorString(e)); return false; }
+        cudaMemcpy(out.data(), d_out, 128 * 128 * 4, cudaMemcpyDeviceToHost);
+        bad = 0;
+        for (int h = 0; h < 2; h++)
+            for (int m = 0; m < 128; m++)
+                for (int n = 0; n < 64; n++) {
+                    double ref = 0;
+                    for (int tap = 0; tap < 9; tap++)
+                        for (int j = 0; j < 4; j++)
+                            for (int kk = 0; kk < 16; kk++) ref += (double)tsval(m, 2 * (tap * 8 + j * 8) + kk) * bval(tap, n, j * 16 + kk);
+                    const double d = fabs(ref - out[(size_t)m * 128 + h * 64 + n]);
+                    if (d > maxerr) maxerr = d;
+                    if (d > 0.5) bad++;
+                }
+    }
+    const int reps = 40;
+    for (int r = 0; r < 2; r++) {
+        k_ts<CP><<<148, 128, SMEM>>>(reps, nullptr, d_cyc);
+        cudaError_t e = cudaDeviceSynchronize();
+        if (e != cudaSuccess) { printf("ts (cp %d) timing: %s\n", CP, cudaGetErrorString(e)); return false; }
+    }
+    cudaMemcpy(cyc.data(), d_cyc, 148 * 8, cudaMemcpyDeviceToHost);
+    double avg = 0;
+    for (int i = 0; i < 148; i++) avg += cyc[i];
+    avg /= 148;
+    printf("ts mode, %2d tcgen05.cp.128x128b per 72 MMAs: mismatches %ld (max err %.1f)   %.1f cycles per MMA (M128 N64 K16), %.0f per 72-MMA tile\n",
+           CP, bad, maxerr, avg / (reps * 72), avg / reps);
+    return true;
+}
+
+void ts_variants(float *d_out, long long *d_cyc)
+{
+    // a failing launch (illegal instruction) poisons the context: stop at the first one
+    if (!run_ts<0>(d_out, d_cyc, true)) return;
+    if (!run_ts<16>(d_out, d_cyc, false)) return;
+    run_ts<24>(d_out, d_cyc, false);
 }
