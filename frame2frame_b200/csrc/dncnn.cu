@@ -554,7 +554,7 @@ k_conv64t(ConvArgs a, const __grid_constant__ CUtensorMap tm_in, const __grid_co
 }
 
 // NHWC BF16 image [H][W][64] as a 3-D tensor (channels, x, y), 128-byte swizzle, box = boxw x boxh pixels
-static int make_tensor_map(CUtensorMap *m, const void *base, int H, int W, int boxw, int boxh)
+int make_tensor_map(CUtensorMap *m, const void *base, int H, int W, int boxw, int boxh)
 {
     const cuuint64_t dims[3] = {64, (cuuint64_t)W, (cuuint64_t)H};
     const cuuint64_t strides[2] = {128, (cuuint64_t)W * 128};

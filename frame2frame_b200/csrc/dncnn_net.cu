@@ -12,6 +12,7 @@
 // Flat parameter vector (the order of DnCNN.state_dict(), 556 032 floats):
 //   conv0.weight[64][1][3][3] | for k = 1..15: conv_k.weight[64][64][3][3], bn_k.weight[64],
 //   bn_k.bias[64] | conv16.weight[1][64][3][3]
+#include <cuda.h>
 #include <cuda_bf16.h>
 #include <stdlib.h>
 #include "f2f_common.cuh"
@@ -19,6 +20,9 @@
 
 namespace f2f {
 extern long g_dncnn_launches;
+namespace dnt {
+int make_tensor_map(CUtensorMap *m, const void *base, int H, int W, int boxw, int boxh);   // dncnn.cu
+}
 namespace net {
 
 using namespace tc05;
@@ -808,9 +812,16 @@ struct Args {
     int pdl_trigger;
     int m64;               // taps ky = 2 as M = 64 instructions (F2F_WGRAD_M64)
     int rev;               // tile order: 1 = bottom-up (f2f_common.cuh, g_tile_rev)
+    int pf;                // L2 prefetch distance, in tiles of a producer group (0: off; F2F_WGRAD_PF)
 };
 
-__global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a)
+// The producers below are register-staged (load -> transform -> one shared-memory store) and were bound by the DRAM
+// latency of their loads.  The three tensor maps are used for NOTHING but cp.async.bulk.prefetch.tensor: before a
+// producer group loads tile t it has the TMA unit pull the boxes of tile t + pf (activation halo box, g box, z box)
+// into L2, clipped at the image edges by the map, so that the ld.global of that tile find their lines in L2.
+__global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a, const __grid_constant__ CUtensorMap tm_act,
+                                                         const __grid_constant__ CUtensorMap tm_g,
+                                                         const __grid_constant__ CUtensorMap tm_z)
 {
     extern __shared__ __align__(1024) uint8_t smem[];
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // provably warp-uniform
@@ -853,9 +864,21 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a)
             sh[j] = a.coef_in ? a.coef_in[C_SHIFT + chunk * 8 + j] : 0.0f;
         }
         const bool bn = a.coef_in != nullptr;
+        const bool pf_lane = a.pf > 0 && pw == 0 && lane == 0;
+        auto prefetch_act = [&](int tf) {
+            if (tf < ntiles) {
+                const int tp = a.rev ? ntiles - 1 - tf : tf;
+                tma_prefetch_l2_3d(&tm_act, 0, (tp % a.tiles_x) * 16 - 1, (tp / a.tiles_x) * TR - 1);
+            }
+        };
+        if (pf_lane) {
+            tma_prefetch_desc(&tm_act);
+            for (int j = 0; j < a.pf; j++) prefetch_act(blockIdx.x + (grp + j * NGROUPS) * gridDim.x);
+        }
         int it = grp;
         for (int tile = blockIdx.x + grp * gridDim.x; tile < ntiles; tile += NGROUPS * gridDim.x, it += NGROUPS) {
             const int s = it % STAGES;
+            if (pf_lane) prefetch_act(tile + a.pf * NGROUPS * gridDim.x);
             mbar_wait(BAR(STAGES + s), ((it / STAGES) & 1) ^ 1);
             uint8_t *dstA = smem + s * STAGE;
             const int tpos = a.rev ? ntiles - 1 - tile : tile;
@@ -927,9 +950,24 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a)
         for (int j = 0; j < 8; j++) {
             cA[j] = a.coef[C_A + chunk * 8 + j]; cB[j] = a.coef[C_B + chunk * 8 + j]; cC[j] = a.coef[C_C + chunk * 8 + j];
         }
+        const bool pf_lane = a.pf > 0 && pw == 4 && lane == 0;
+        auto prefetch_dz = [&](int tf) {
+            if (tf < ntiles) {
+                const int tp = a.rev ? ntiles - 1 - tf : tf;
+                const int px = (tp % a.tiles_x) * 16, py = (tp / a.tiles_x) * TR;
+                tma_prefetch_l2_3d(&tm_g, 0, px, py);
+                tma_prefetch_l2_3d(&tm_z, 0, px, py);
+            }
+        };
+        if (pf_lane) {
+            tma_prefetch_desc(&tm_g);
+            tma_prefetch_desc(&tm_z);
+            for (int j = 0; j < a.pf; j++) prefetch_dz(blockIdx.x + (grp + j * NGROUPS) * gridDim.x);
+        }
         int it = grp;
         for (int tile = blockIdx.x + grp * gridDim.x; tile < ntiles; tile += NGROUPS * gridDim.x, it += NGROUPS) {
             const int s = it % STAGES;
+            if (pf_lane) prefetch_dz(tile + a.pf * NGROUPS * gridDim.x);
             mbar_wait(BAR(STAGES + s), ((it / STAGES) & 1) ^ 1);
             uint8_t *dstD = smem + s * STAGE + A_BYTES;
             const int tpos = a.rev ? ntiles - 1 - tile : tile;
@@ -1095,7 +1133,15 @@ static int wgrad64_scaled(const void *d_act, const float *d_coef_in, void *d_g, 
     static const int m64 = getenv("F2F_WGRAD_M64") ? atoi(getenv("F2F_WGRAD_M64")) : 1;   // 0: M = 128 throughout (A/B, profiles/r01_m64_ab.log)
     a.m64 = m64;
     a.rev = g_tile_rev;
-    F2F_CUDA_CHECK(launch_pdl(1, wg::k_wgrad64, dim3(grid), dim3(wg::NTHREADS), wg::SMEM_BYTES, st, a));
+    // L2 prefetch distance of the producers (tiles of a producer group); 0 turns the prefetches off (A/B)
+    static const int pf = getenv("F2F_WGRAD_PF") ? atoi(getenv("F2F_WGRAD_PF")) : 2;
+    a.pf = pf < 0 ? 0 : pf > 8 ? 8 : pf;
+    CUtensorMap tm_act, tm_g, tm_z;
+    int rc = dnt::make_tensor_map(&tm_act, d_act, H, W, 18, wg::HR);
+    if (!rc) rc = dnt::make_tensor_map(&tm_g, d_g, H, W, 16, wg::TR);
+    if (!rc) rc = dnt::make_tensor_map(&tm_z, d_z, H, W, 16, wg::TR);
+    if (rc) return rc;
+    F2F_CUDA_CHECK(launch_pdl(1, wg::k_wgrad64, dim3(grid), dim3(wg::NTHREADS), wg::SMEM_BYTES, st, a, tm_act, tm_g, tm_z));
     prof_end(1, st);
     F2F_CUDA_CHECK(launch_pdl(0, wg::k_wgrad_reduce, dim3(cdiv(9 * 4096, 256)), dim3(256), 0, st, (const float *)d_partial, grid,
                               d_dw, accumulate, (g_pdl >> 3) & 1, d_absmax, extra_scale));

@@ -71,6 +71,13 @@ __device__ __forceinline__ void tma_prefetch_desc(const void *tmap)
 {
     asm volatile("prefetch.tensormap [%0];" ::"l"(tmap) : "memory");
 }
+// the same box brought into L2 only (no shared-memory destination, no barrier): the TMA unit walks the tile, clips it
+// at the tensor's edges, and later loads of those bytes -- by TMA or by plain ld.global -- hit L2
+__device__ __forceinline__ void tma_prefetch_l2_3d(const void *tmap, int c0, int c1, int c2)
+{
+    asm volatile("cp.async.bulk.prefetch.tensor.3d.L2.global.tile [%0, {%1, %2, %3}];" ::"l"(tmap), "r"(c0), "r"(c1), "r"(c2)
+                 : "memory");
+}
 
 // ------------------------------------------------------------------- TMEM
 __device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols)
