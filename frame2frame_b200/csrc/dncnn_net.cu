@@ -403,6 +403,28 @@ struct LossFuse {
     float inv_n;
 };
 
+// MMA = true (the default, F2F_LAST_MMA=0 restores the CUDA-core version): the per-pixel dot products run on the tensor
+// cores as warp-level mma.sync m16n8k16 -- P[16 pixels][taps] += A[16 pixels][16 channels] * Wt[16 channels][8 taps],
+// FP32 accumulate.  The layer is HBM-bound (128 bytes in, 4 out per pixel; N = 9 is far too narrow for tcgen05), the
+// point is to take the 640 FMAs and 150 warp-uniform shared-memory loads per pixel and lane off the CUDA cores, which
+// held the scalar version at 2.5x its HBM time.  A lane (g = lane / 4, t = lane % 4) loads channels [8t, 8t+8) and
+// [32+8t, 32+8t+8) of pixels g and g+8 of a 16-pixel group (four 16-byte loads, every byte of the two 128-byte pixel
+// rows used once), applies layer 15's BatchNorm+ReLU in FP32 and rounds to the 16-bit storage type -- the operand
+// rounding every 64->64 layer applies to its input (dnt::k_conv64t) -- and feeds the words to the A fragment as they
+// lie: the contraction does not care which channel sits in which k slot as long as the B fragment (built once per
+// kernel from w16, rounded to 16 bits like the other layers' weights) uses the same assignment.
+__device__ __forceinline__ void mma16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1)
+{
+#ifndef F2F_STORE_BF16
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+#else
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+#endif
+                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+template <bool MMA>
 __global__ void __launch_bounds__(256) k_last_fwd(const h16 *__restrict__ z, const float *__restrict__ coef,
                                                   const float *__restrict__ w16, const float *__restrict__ x,
                                                   float *__restrict__ out, int H, int W, int tiles_x, int ntiles, int residual,
@@ -410,20 +432,102 @@ __global__ void __launch_bounds__(256) k_last_fwd(const h16 *__restrict__ z, con
 {
     double lacc = 0.0;
     unsigned amax = 0;
-    __shared__ float T[LHP * 9 + 4];
-    __shared__ __align__(16) float wS[8 * 72];          // [chunk][tap][8 channels]
-    __shared__ __align__(16) float cS[128];             // scale[64], shift[64]
-    for (int e = threadIdx.x; e < 8 * 72; e += 256) {
-        const int c = e / 72, t = (e % 72) >> 3, j = e & 7;
-        wS[e] = w16[(c * 8 + j) * 9 + t];
+    constexpr int TS = MMA ? 10 : 9;                    // floats per pixel of T (10: 8-byte aligned pair stores)
+    __shared__ __align__(16) float T[LHP * TS + 4];
+    __shared__ __align__(16) float wS[MMA ? 4 : 8 * 72];          // [chunk][tap][8 channels]
+    __shared__ __align__(16) float cS[MMA ? 4 : 128];             // scale[64], shift[64]
+    // MMA: this lane's 16 channels are c(h, j) = 32h + 8t + j; k-step (h, e) puts channels 4e + {0,1} in k slots
+    // 2t + {0,1} and channels 4e + {2,3} in k slots 2t + 8 + {0,1}
+    [[maybe_unused]] float sc[16], sh[16];
+    [[maybe_unused]] uint32_t bw[4][2][2];              // B fragments: [k-step][n tile: taps 0-7 | tap 8][register]
+    if constexpr (MMA) {
+        const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+#pragma unroll
+        for (int h = 0; h < 2; h++)
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                sc[h * 8 + j] = coef[C_SCALE + 32 * h + 8 * t + j];
+                sh[h * 8 + j] = coef[C_SHIFT + 32 * h + 8 * t + j];
+            }
+#pragma unroll
+        for (int ks = 0; ks < 4; ks++)
+#pragma unroll
+            for (int nt = 0; nt < 2; nt++) {
+                const int tap = nt * 8 + g, c = 32 * (ks >> 1) + 8 * t + 4 * (ks & 1);
+                const bool live = tap < 9;
+                bw[ks][nt][0] = live ? pack_h16(w16[(c + 0) * 9 + tap], w16[(c + 1) * 9 + tap]) : 0u;
+                bw[ks][nt][1] = live ? pack_h16(w16[(c + 2) * 9 + tap], w16[(c + 3) * 9 + tap]) : 0u;
+            }
+    } else {
+        for (int e = threadIdx.x; e < 8 * 72; e += 256) {
+            const int c = e / 72, t = (e % 72) >> 3, j = e & 7;
+            wS[e] = w16[(c * 8 + j) * 9 + t];
+        }
+        if (threadIdx.x < 64) { cS[threadIdx.x] = coef[C_SCALE + threadIdx.x]; cS[64 + threadIdx.x] = coef[C_SHIFT + threadIdx.x]; }
     }
-    if (threadIdx.x < 64) { cS[threadIdx.x] = coef[C_SCALE + threadIdx.x]; cS[64 + threadIdx.x] = coef[C_SHIFT + threadIdx.x]; }
     __syncthreads();
     const float4 *wv = reinterpret_cast<const float4 *>(wS), *cv = reinterpret_cast<const float4 *>(cS);
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         const int ty0 = (tile / tiles_x) * LT, tx0 = (tile % tiles_x) * LT;
+        if constexpr (MMA) {
+            const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
+            constexpr int NG = (LHP + 15) / 16;          // 16-pixel groups of the haloed tile; warp w takes w, w+8, w+16
+            uint4 v[3][2][2];                            // [group][pixel g | g+8][channel half]
+            // all loads of the warp's groups first (12 x 16 bytes per lane in flight)
+#pragma unroll
+            for (int q = 0; q < 3; q++)
+#pragma unroll
+                for (int r = 0; r < 2; r++) {
+                    const int pix = (warp + 8 * q) * 16 + g + 8 * r;
+                    const int gy = ty0 - 1 + pix / LH, gx = tx0 - 1 + pix % LH;
+                    v[q][r][0] = v[q][r][1] = make_uint4(0, 0, 0, 0);
+                    if (warp + 8 * q < NG && pix < LHP && gy >= 0 && gy < H && gx >= 0 && gx < W) {
+                        const uint4 *src = reinterpret_cast<const uint4 *>(z + ((size_t)gy * W + gx) * 64);
+                        v[q][r][0] = __ldg(src + t);
+                        v[q][r][1] = __ldg(src + 4 + t);
+                    }
+                }
+#pragma unroll
+            for (int q = 0; q < 3; q++) {
+                if (warp + 8 * q >= NG) break;           // warp-uniform
+                uint32_t aw[2][2][4];                    // [pixel][half][word]: BatchNorm + ReLU, rounded to 16 bits
+#pragma unroll
+                for (int r = 0; r < 2; r++) {
+                    const int pix = (warp + 8 * q) * 16 + g + 8 * r;
+                    const int gy = ty0 - 1 + pix / LH, gx = tx0 - 1 + pix % LH;
+                    const bool in = pix < LHP && gy >= 0 && gy < H && gx >= 0 && gx < W;   // zero padding is of a15, not of z15
+#pragma unroll
+                    for (int h = 0; h < 2; h++) {
+                        const uint32_t w4[4] = {v[q][r][h].x, v[q][r][h].y, v[q][r][h].z, v[q][r][h].w};
+#pragma unroll
+                        for (int j = 0; j < 4; j++) {
+                            const float2 f = unpack_h16(w4[j]);
+                            const uint32_t pk = pack_h16_relu(fmaf(f.x, sc[h * 8 + 2 * j], sh[h * 8 + 2 * j]),
+                                                              fmaf(f.y, sc[h * 8 + 2 * j + 1], sh[h * 8 + 2 * j + 1]));
+                            aw[r][h][j] = in ? pk : 0u;
+                        }
+                    }
+                }
+                float d0[4] = {0.f, 0.f, 0.f, 0.f}, d1[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                for (int ks = 0; ks < 4; ks++) {
+                    const int h = ks >> 1, e = ks & 1;
+                    mma16816(d0, aw[0][h][2 * e], aw[1][h][2 * e], aw[0][h][2 * e + 1], aw[1][h][2 * e + 1], bw[ks][0][0], bw[ks][0][1]);
+                    mma16816(d1, aw[0][h][2 * e], aw[1][h][2 * e], aw[0][h][2 * e + 1], aw[1][h][2 * e + 1], bw[ks][1][0], bw[ks][1][1]);
+                }
+                // accumulator (row g: d[0], d[1]; row g+8: d[2], d[3]) holds taps 2t, 2t+1 of its n tile
+#pragma unroll
+                for (int r = 0; r < 2; r++) {
+                    const int pix = (warp + 8 * q) * 16 + g + 8 * r;
+                    if (pix < LHP) {
+                        *reinterpret_cast<float2 *>(&T[pix * TS + 2 * t]) = make_float2(d0[2 * r], d0[2 * r + 1]);
+                        if (t == 0) T[pix * TS + 8] = d1[2 * r];
+                    }
+                }
+            }
+        }
 #pragma unroll 1
-        for (int pix = threadIdx.x; pix < LHP; pix += 256) {
+        for (int pix = threadIdx.x; !MMA && pix < LHP; pix += 256) {
             const int gy = ty0 - 1 + pix / LH, gx = tx0 - 1 + pix % LH;
             float part[9];
 #pragma unroll
@@ -455,7 +559,7 @@ __global__ void __launch_bounds__(256) k_last_fwd(const h16 *__restrict__ z, con
                 }
             }
 #pragma unroll
-            for (int t = 0; t < 9; t++) T[pix * 9 + t] = part[t];
+            for (int t = 0; t < 9; t++) T[pix * TS + t] = part[t];
         }
         __syncthreads();
         {
@@ -463,7 +567,7 @@ __global__ void __launch_bounds__(256) k_last_fwd(const h16 *__restrict__ z, con
             const int gy = ty0 + y, gx = tx0 + xx;
             float n = 0.0f;
 #pragma unroll
-            for (int t = 0; t < 9; t++) n += T[((y + t / 3) * LH + xx + t % 3) * 9 + t];
+            for (int t = 0; t < 9; t++) n += T[((y + t / 3) * LH + xx + t % 3) * TS + t];
             if (gy < H && gx < W) {
                 const size_t i = (size_t)gy * W + gx;
                 const float o = residual ? x[i] - n : n;
@@ -813,7 +917,14 @@ struct Args {
     int m64;               // taps ky = 2 as M = 64 instructions (F2F_WGRAD_M64)
     int rev;               // tile order: 1 = bottom-up (f2f_common.cuh, g_tile_rev)
     int pf;                // L2 prefetch distance, in tiles of a producer group (0: off; F2F_WGRAD_PF)
+    int dbg;               // -DF2F_WG_DEBUG builds only (tools/perf_wgrad.py): bit 0 no MMAs, 1 no activation loads,
+                           // 2 no g/z loads, 3 no dz write-back, 4 no shared-memory stores, 5 no transform arithmetic
 };
+#ifdef F2F_WG_DEBUG
+#define WG_DBG(bit) ((a.dbg >> (bit)) & 1)
+#else
+#define WG_DBG(bit) 0
+#endif
 
 // The producers below are register-staged (load -> transform -> one shared-memory store) and were bound by the DRAM
 // latency of their loads.  The three tensor maps are used for NOTHING but cp.async.bulk.prefetch.tensor: before a
@@ -891,7 +1002,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a, const __grid_co
                 const int pix = (ptid >> 3) + 16 * u;
                 const int gy = ty0 + pix / 18, gx = tx0 + pix % 18;
                 v[u] = make_uint4(0, 0, 0, 0);
-                if (pix < HPIX && gy >= 0 && gy < a.H && gx >= 0 && gx < a.W) {
+                if (pix < HPIX && gy >= 0 && gy < a.H && gx >= 0 && gx < a.W && !WG_DBG(1)) {
                     inb |= 1u << u;
                     v[u] = __ldg(reinterpret_cast<const uint4 *>(a.act + ((size_t)gy * a.W + gx) * 64 + chunk * 8));
                 }
@@ -901,7 +1012,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a, const __grid_co
                 const int pix = (ptid >> 3) + 16 * u;
                 if (pix < HPIX) {
                     uint4 o = v[u];
-                    if (bn && ((inb >> u) & 1u)) {
+                    if (bn && ((inb >> u) & 1u) && !WG_DBG(5)) {
                         uint32_t w[4] = {o.x, o.y, o.z, o.w};
 #pragma unroll
                         for (int j = 0; j < 4; j++) {
@@ -910,7 +1021,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a, const __grid_co
                         }
                         o = make_uint4(w[0], w[1], w[2], w[3]);
                     }
-                    *reinterpret_cast<uint4 *>(dstA + (pix / 18) * A_R + chunk * A_S + (pix % 18) * 16) = o;
+                    if (!WG_DBG(4)) *reinterpret_cast<uint4 *>(dstA + (pix / 18) * A_R + chunk * A_S + (pix % 18) * 16) = o;
                 }
             }
             fence_proxy_async();
@@ -982,7 +1093,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a, const __grid_co
                 const int pix = (ptid >> 3) + 16 * (r0 + u);
                 const int gy = ty0 + (pix >> 4), gx = tx0 + (pix & 15);
                 vg[u] = vz[u] = make_uint4(0, 0, 0, 0);
-                if (gy < a.H && gx < a.W) {
+                if (gy < a.H && gx < a.W && !WG_DBG(2)) {
                     inb |= 1u << u;
                     const size_t o = ((size_t)gy * a.W + gx) * 64 + chunk * 8;
                     vg[u] = *reinterpret_cast<const uint4 *>(a.g + o);
@@ -996,18 +1107,19 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a, const __grid_co
                 if ((inb >> u) & 1u) {
                     const uint32_t gw[4] = {vg[u].x, vg[u].y, vg[u].z, vg[u].w};
                     const uint32_t zw[4] = {vz[u].x, vz[u].y, vz[u].z, vz[u].w};
-                    uint32_t w[4];
+                    uint32_t w[4] = {gw[0], gw[1], gw[2], gw[3]};
 #pragma unroll
                     for (int j = 0; j < 4; j++) {
+                        if (WG_DBG(5)) break;
                         const float2 gg = unpack_h16(gw[j]), zz = unpack_h16(zw[j]);
                         w[j] = pack_h16(fmaf(cA[2 * j], gg.x, fmaf(cB[2 * j], zz.x, cC[2 * j])),
                                          fmaf(cA[2 * j + 1], gg.y, fmaf(cB[2 * j + 1], zz.y, cC[2 * j + 1])));
                     }
                     o = make_uint4(w[0], w[1], w[2], w[3]);
                     const int gy = ty0 + (pix >> 4), gx = tx0 + (pix & 15);
-                    *reinterpret_cast<uint4 *>(a.g + ((size_t)gy * a.W + gx) * 64 + chunk * 8) = o;
+                    if (!WG_DBG(3)) *reinterpret_cast<uint4 *>(a.g + ((size_t)gy * a.W + gx) * 64 + chunk * 8) = o;
                 }
-                *reinterpret_cast<uint4 *>(dstD + (pix >> 4) * D_R + chunk * D_S + (pix & 15) * 16) = o;
+                if (!WG_DBG(4)) *reinterpret_cast<uint4 *>(dstD + (pix >> 4) * D_R + chunk * D_S + (pix & 15) * 16) = o;
             }
             }
             fence_proxy_async();
@@ -1032,6 +1144,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a, const __grid_co
             const uint32_t b_lo = (uint32_t)bd0 | (((a_base + A_BYTES) & 0x3FFFFu) >> 4);
 #pragma unroll
             for (int r = 0; r < TR; r++) {
+                if (WG_DBG(0)) break;
                 const uint64_t bd = ((uint64_t)b_hi << 32) | (b_lo + r * (D_R / 16));
 #pragma unroll
                 for (int j = 0; j < 6; j++) {
@@ -1136,6 +1249,7 @@ static int wgrad64_scaled(const void *d_act, const float *d_coef_in, void *d_g, 
     // L2 prefetch distance of the producers (tiles of a producer group); 0 turns the prefetches off (A/B)
     static const int pf = getenv("F2F_WGRAD_PF") ? atoi(getenv("F2F_WGRAD_PF")) : 2;
     a.pf = pf < 0 ? 0 : pf > 8 ? 8 : pf;
+    a.dbg = getenv("F2F_WGRAD_DBG") ? atoi(getenv("F2F_WGRAD_DBG")) : 0;
     CUtensorMap tm_act, tm_g, tm_z;
     int rc = dnt::make_tensor_map(&tm_act, d_act, H, W, 18, wg::HR);
     if (!rc) rc = dnt::make_tensor_map(&tm_g, d_g, H, W, 16, wg::TR);
@@ -1303,7 +1417,8 @@ static int forward_impl(const float *d_params, float *d_bn_running, long long *d
             if (rc) return rc;
             continue;
         }
-        rs::k_last_fwd<<<ntiles < simt_blocks() ? ntiles : simt_blocks(), 256, 0, st>>>(
+        static const int last_mma = getenv("F2F_LAST_MMA") ? atoi(getenv("F2F_LAST_MMA")) : 1;   // 0: CUDA-core version (A/B)
+        (last_mma ? rs::k_last_fwd<true> : rs::k_last_fwd<false>)<<<ntiles < simt_blocks() ? ntiles : simt_blocks(), 256, 0, st>>>(
             zbuf(NBN) + b * P * 64, coef + (size_t)(NBN - 1) * C_STRIDE, d_params + OFF_W16, d_x + b * P, d_y + b * P, H, W,
             tiles_x, ntiles, residual, lf);
         g_dncnn_launches++;
