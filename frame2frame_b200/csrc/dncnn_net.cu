@@ -20,6 +20,7 @@
 
 namespace f2f {
 extern long g_dncnn_launches;
+namespace dn { extern unsigned long long *g_conv_trace; }
 namespace dnt {
 int make_tensor_map(CUtensorMap *m, const void *base, int H, int W, int boxw, int boxh);   // dncnn.cu
 }
@@ -407,12 +408,13 @@ struct LossFuse {
 // cores as warp-level mma.sync m16n8k16 -- P[16 pixels][taps] += A[16 pixels][16 channels] * Wt[16 channels][8 taps],
 // FP32 accumulate.  The layer is HBM-bound (128 bytes in, 4 out per pixel; N = 9 is far too narrow for tcgen05), the
 // point is to take the 640 FMAs and 150 warp-uniform shared-memory loads per pixel and lane off the CUDA cores, which
-// held the scalar version at 2.5x its HBM time.  A lane (g = lane / 4, t = lane % 4) loads channels [8t, 8t+8) and
-// [32+8t, 32+8t+8) of pixels g and g+8 of a 16-pixel group (four 16-byte loads, every byte of the two 128-byte pixel
-// rows used once), applies layer 15's BatchNorm+ReLU in FP32 and rounds to the 16-bit storage type -- the operand
-// rounding every 64->64 layer applies to its input (dnt::k_conv64t) -- and feeds the words to the A fragment as they
-// lie: the contraction does not care which channel sits in which k slot as long as the B fragment (built once per
-// kernel from w16, rounded to 16 bits like the other layers' weights) uses the same assignment.
+// held the scalar version at 2.5x its HBM time.  A lane (g = lane / 4, t = lane % 4) loads channels [16t, 16t+16)
+// of pixels g and g+8 of a 16-pixel group (two 32-byte loads, every byte of the two 128-byte pixel rows used once), applies layer 15's BatchNorm+ReLU in FP32 and splits the result into a 16-bit value and the 16-bit
+// remainder, as the weights are split once per kernel: three products (hi*hi, lo*hi, hi*lo) keep the layer at FP32-class
+// precision like the CUDA-core version -- with single 16-bit operands the config0 trajectory of the online loop moved
+// by 0.06 dB on the second frame, past the 0.05 dB bar the default mode is held to there; the MMAs are nearly free in
+// this HBM-bound kernel.  The words feed the A fragment as they lie: the contraction does not care which channel sits
+// in which k slot as long as the B fragment uses the same assignment.
 __device__ __forceinline__ void mma16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1)
 {
 #ifndef F2F_STORE_BF16
@@ -425,7 +427,7 @@ __device__ __forceinline__ void mma16816(float (&d)[4], uint32_t a0, uint32_t a1
 }
 
 template <bool MMA>
-__global__ void __launch_bounds__(256) k_last_fwd(const h16 *__restrict__ z, const float *__restrict__ coef,
+__global__ void __launch_bounds__(256, MMA ? 2 : 1) k_last_fwd(const h16 *__restrict__ z, const float *__restrict__ coef,
                                                   const float *__restrict__ w16, const float *__restrict__ x,
                                                   float *__restrict__ out, int H, int W, int tiles_x, int ntiles, int residual,
                                                   LossFuse lf)
@@ -436,28 +438,34 @@ __global__ void __launch_bounds__(256) k_last_fwd(const h16 *__restrict__ z, con
     __shared__ __align__(16) float T[LHP * TS + 4];
     __shared__ __align__(16) float wS[MMA ? 4 : 8 * 72];          // [chunk][tap][8 channels]
     __shared__ __align__(16) float cS[MMA ? 4 : 128];             // scale[64], shift[64]
-    // MMA: this lane's 16 channels are c(h, j) = 32h + 8t + j; k-step (h, e) puts channels 4e + {0,1} in k slots
+    // MMA: this lane's 16 channels are c(h, j) = 16t + 8h + j; k-step (h, e) puts channels 4e + {0,1} in k slots
     // 2t + {0,1} and channels 4e + {2,3} in k slots 2t + 8 + {0,1}
-    [[maybe_unused]] float sc[16], sh[16];
-    [[maybe_unused]] uint32_t bw[4][2][2];              // B fragments: [k-step][n tile: taps 0-7 | tap 8][register]
+    __shared__ __align__(16) float cT[MMA ? 4 * 32 : 4];         // MMA: [t][scale of the lane's 16 channels | shift of them]
+    // B fragments [k-step][register] of taps 0-7: w16 as a 16-bit hi part and the 16-bit remainder; tap 8 does not fit the
+    // N = 8 tile and a second tile for one column doubles the mma.sync count, which bounds this kernel: it is an FP32
+    // dot product over the lane's 16 channels and a 4-lane shuffle sum
+    [[maybe_unused]] uint32_t bw[4][2], bl[4][2];
+    [[maybe_unused]] float w8[16];
     if constexpr (MMA) {
         const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+        if (threadIdx.x < 128) {                         // coefficient table: the registers are needed for the fragments
+            const int tt = threadIdx.x >> 5, i = threadIdx.x & 31, cc = 16 * tt + (i & 15);
+            cT[threadIdx.x] = coef[(i < 16 ? C_SCALE : C_SHIFT) + cc];
+        }
 #pragma unroll
-        for (int h = 0; h < 2; h++)
+        for (int ks = 0; ks < 4; ks++) {
+            const int tap = g, c = 16 * t + 8 * (ks >> 1) + 4 * (ks & 1);
 #pragma unroll
-            for (int j = 0; j < 8; j++) {
-                sc[h * 8 + j] = coef[C_SCALE + 32 * h + 8 * t + j];
-                sh[h * 8 + j] = coef[C_SHIFT + 32 * h + 8 * t + j];
+            for (int i = 0; i < 2; i++) {
+                const float w0 = w16[(c + 2 * i) * 9 + tap], w1 = w16[(c + 2 * i + 1) * 9 + tap];
+                const uint32_t hi = pack_h16(w0, w1);
+                const float2 hf = unpack_h16(hi);
+                bw[ks][i] = hi;
+                bl[ks][i] = pack_h16(w0 - hf.x, w1 - hf.y);
             }
+        }
 #pragma unroll
-        for (int ks = 0; ks < 4; ks++)
-#pragma unroll
-            for (int nt = 0; nt < 2; nt++) {
-                const int tap = nt * 8 + g, c = 32 * (ks >> 1) + 8 * t + 4 * (ks & 1);
-                const bool live = tap < 9;
-                bw[ks][nt][0] = live ? pack_h16(w16[(c + 0) * 9 + tap], w16[(c + 1) * 9 + tap]) : 0u;
-                bw[ks][nt][1] = live ? pack_h16(w16[(c + 2) * 9 + tap], w16[(c + 3) * 9 + tap]) : 0u;
-            }
+        for (int i = 0; i < 16; i++) w8[i] = w16[(16 * t + i) * 9 + 8];
     } else {
         for (int e = threadIdx.x; e < 8 * 72; e += 256) {
             const int c = e / 72, t = (e % 72) >> 3, j = e & 7;
@@ -467,30 +475,47 @@ __global__ void __launch_bounds__(256) k_last_fwd(const h16 *__restrict__ z, con
     }
     __syncthreads();
     const float4 *wv = reinterpret_cast<const float4 *>(wS), *cv = reinterpret_cast<const float4 *>(cS);
+    // MMA: operand registers of two 16-pixel groups [slot][pixel g | g+8][channel half].  (Issuing the next tile's first
+    // loads before this tile's output stage was tried and was slower, 167 against 143 us: the kernel is bound by the
+    // mma.sync rate, not by load latency.)
+    [[maybe_unused]] uint4 v[2][2][2];
+    [[maybe_unused]] auto load_group = [&](int tl, int q, uint4 (&dst)[2][2]) {
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
+        const int by = (tl / tiles_x) * LT - 1, bx = (tl % tiles_x) * LT - 1;
+#pragma unroll
+        for (int r = 0; r < 2; r++) {
+            const int pix = (warp + 8 * q) * 16 + g + 8 * r;
+            const int gy = by + pix / LH, gx = bx + pix % LH;
+            dst[r][0] = dst[r][1] = make_uint4(0, 0, 0, 0);
+            if (pix < LHP && gy >= 0 && gy < H && gx >= 0 && gx < W) {
+                // one 32-byte load: the four lanes of a pixel cover its 128-byte line once (two 16-byte loads at a
+                // 64-byte distance had every warp-wide load touch eight half-used lines: ncu showed L1 at 83 %)
+                ldg256(z + ((size_t)gy * W + gx) * 64 + 16 * t, dst[r][0], dst[r][1]);
+            }
+        }
+    };
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         const int ty0 = (tile / tiles_x) * LT, tx0 = (tile % tiles_x) * LT;
+        // this thread's output pixel: its x / mask / warped values are fetched now, so that their latency passes under
+        // the partial products instead of after the barrier
+        const int oy = ty0 + (threadIdx.x >> 4), ox = tx0 + (threadIdx.x & 15);
+        const bool oin = oy < H && ox < W;
+        const size_t oi = (size_t)oy * W + ox;
+        float xin = 0.0f, min_ = 0.0f, win = 0.0f;
+        if (oin) {
+            if (residual) xin = __ldg(x + oi);
+            if (lf.warped) { min_ = __ldg(lf.mask + oi); win = __ldg(lf.warped + oi); }
+        }
         if constexpr (MMA) {
             const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
             constexpr int NG = (LHP + 15) / 16;          // 16-pixel groups of the haloed tile; warp w takes w, w+8, w+16
-            uint4 v[3][2][2];                            // [group][pixel g | g+8][channel half]
-            // all loads of the warp's groups first (12 x 16 bytes per lane in flight)
-#pragma unroll
-            for (int q = 0; q < 3; q++)
-#pragma unroll
-                for (int r = 0; r < 2; r++) {
-                    const int pix = (warp + 8 * q) * 16 + g + 8 * r;
-                    const int gy = ty0 - 1 + pix / LH, gx = tx0 - 1 + pix % LH;
-                    v[q][r][0] = v[q][r][1] = make_uint4(0, 0, 0, 0);
-                    if (warp + 8 * q < NG && pix < LHP && gy >= 0 && gy < H && gx >= 0 && gx < W) {
-                        const uint4 *src = reinterpret_cast<const uint4 *>(z + ((size_t)gy * W + gx) * 64);
-                        v[q][r][0] = __ldg(src + t);
-                        v[q][r][1] = __ldg(src + 4 + t);
-                    }
-                }
+            load_group(tile, 0, v[0]);
+            load_group(tile, 1, v[1]);                   // two groups (8 x 16 bytes per lane) in flight
 #pragma unroll
             for (int q = 0; q < 3; q++) {
-                if (warp + 8 * q >= NG) break;           // warp-uniform
-                uint32_t aw[2][2][4];                    // [pixel][half][word]: BatchNorm + ReLU, rounded to 16 bits
+                if (warp + 8 * q >= NG) break;           // warp-uniform (warps 5-7 have no third group)
+                uint32_t aw[2][2][4], al[2][2][4];       // [pixel][half][word]: BatchNorm + ReLU in FP32 as 16-bit hi + remainder
+                float p8[2] = {0.0f, 0.0f};              // tap 8 of the two pixels, this lane's 16 channels (CUDA cores)
 #pragma unroll
                 for (int r = 0; r < 2; r++) {
                     const int pix = (warp + 8 * q) * 16 + g + 8 * r;
@@ -498,22 +523,39 @@ __global__ void __launch_bounds__(256) k_last_fwd(const h16 *__restrict__ z, con
                     const bool in = pix < LHP && gy >= 0 && gy < H && gx >= 0 && gx < W;   // zero padding is of a15, not of z15
 #pragma unroll
                     for (int h = 0; h < 2; h++) {
-                        const uint32_t w4[4] = {v[q][r][h].x, v[q][r][h].y, v[q][r][h].z, v[q][r][h].w};
+                        const uint32_t w4[4] = {v[q & 1][r][h].x, v[q & 1][r][h].y, v[q & 1][r][h].z, v[q & 1][r][h].w};
+                        const float4 *ct = reinterpret_cast<const float4 *>(cT + t * 32 + h * 8);
+                        const float4 s0 = ct[0], s1 = ct[1], h0 = ct[4], h1 = ct[5];
+                        const float scv[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+                        const float shv[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
 #pragma unroll
                         for (int j = 0; j < 4; j++) {
                             const float2 f = unpack_h16(w4[j]);
-                            const uint32_t pk = pack_h16_relu(fmaf(f.x, sc[h * 8 + 2 * j], sh[h * 8 + 2 * j]),
-                                                              fmaf(f.y, sc[h * 8 + 2 * j + 1], sh[h * 8 + 2 * j + 1]));
+                            const float a0 = fmaxf(fmaf(f.x, scv[2 * j], shv[2 * j]), 0.0f);
+                            const float a1 = fmaxf(fmaf(f.y, scv[2 * j + 1], shv[2 * j + 1]), 0.0f);
+                            const uint32_t pk = pack_h16(a0, a1);
+                            const float2 hf = unpack_h16(pk);
                             aw[r][h][j] = in ? pk : 0u;
+                            al[r][h][j] = in ? pack_h16(a0 - hf.x, a1 - hf.y) : 0u;
+                            if (in) p8[r] = fmaf(a0, w8[h * 8 + 2 * j], fmaf(a1, w8[h * 8 + 2 * j + 1], p8[r]));
                         }
                     }
                 }
-                float d0[4] = {0.f, 0.f, 0.f, 0.f}, d1[4] = {0.f, 0.f, 0.f, 0.f};
+                if (q == 0) load_group(tile, 2, v[0]);   // group 0's registers are free again
+                float d0[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
                 for (int ks = 0; ks < 4; ks++) {
                     const int h = ks >> 1, e = ks & 1;
-                    mma16816(d0, aw[0][h][2 * e], aw[1][h][2 * e], aw[0][h][2 * e + 1], aw[1][h][2 * e + 1], bw[ks][0][0], bw[ks][0][1]);
-                    mma16816(d1, aw[0][h][2 * e], aw[1][h][2 * e], aw[0][h][2 * e + 1], aw[1][h][2 * e + 1], bw[ks][1][0], bw[ks][1][1]);
+                    // a * w = (ah + al) * (wh + wl) without the al * wl term (2^-22 relative): the small products first
+                    mma16816(d0, al[0][h][2 * e], al[1][h][2 * e], al[0][h][2 * e + 1], al[1][h][2 * e + 1], bw[ks][0], bw[ks][1]);
+                    mma16816(d0, aw[0][h][2 * e], aw[1][h][2 * e], aw[0][h][2 * e + 1], aw[1][h][2 * e + 1], bl[ks][0], bl[ks][1]);
+                    mma16816(d0, aw[0][h][2 * e], aw[1][h][2 * e], aw[0][h][2 * e + 1], aw[1][h][2 * e + 1], bw[ks][0], bw[ks][1]);
+                }
+                // tap 8: the four lanes of a pixel row hold disjoint channel sets
+#pragma unroll
+                for (int r = 0; r < 2; r++) {
+                    p8[r] += __shfl_xor_sync(0xffffffffu, p8[r], 1);
+                    p8[r] += __shfl_xor_sync(0xffffffffu, p8[r], 2);
                 }
                 // accumulator (row g: d[0], d[1]; row g+8: d[2], d[3]) holds taps 2t, 2t+1 of its n tile
 #pragma unroll
@@ -521,7 +563,7 @@ __global__ void __launch_bounds__(256) k_last_fwd(const h16 *__restrict__ z, con
                     const int pix = (warp + 8 * q) * 16 + g + 8 * r;
                     if (pix < LHP) {
                         *reinterpret_cast<float2 *>(&T[pix * TS + 2 * t]) = make_float2(d0[2 * r], d0[2 * r + 1]);
-                        if (t == 0) T[pix * TS + 8] = d1[2 * r];
+                        if (t == 0) T[pix * TS + 8] = p8[r];
                     }
                 }
             }
@@ -564,17 +606,16 @@ __global__ void __launch_bounds__(256) k_last_fwd(const h16 *__restrict__ z, con
         __syncthreads();
         {
             const int y = threadIdx.x >> 4, xx = threadIdx.x & 15;
-            const int gy = ty0 + y, gx = tx0 + xx;
             float n = 0.0f;
 #pragma unroll
             for (int t = 0; t < 9; t++) n += T[((y + t / 3) * LH + xx + t % 3) * TS + t];
-            if (gy < H && gx < W) {
-                const size_t i = (size_t)gy * W + gx;
-                const float o = residual ? x[i] - n : n;
+            if (oin) {
+                const size_t i = oi;
+                const float o = residual ? xin - n : n;
                 out[i] = o;
                 if (lf.warped) {                       // blind_denoising.py:121 / warped_loss.py:227,239-248, as k_masked_loss
-                    const float m = lf.mask[i];
-                    const float d = __fsub_rn(__fmul_rn(m, o), __fmul_rn(m, lf.warped[i]));
+                    const float m = min_;
+                    const float d = __fsub_rn(__fmul_rn(m, o), __fmul_rn(m, win));
                     float g;
                     if (lf.kind == 0) {
                         lacc += (double)fabsf(d);
@@ -881,6 +922,9 @@ static int first_wgrad(int C, const T *g0, const float *x, double *dw0, int H, i
 // k_bn_bwd_coeffs) from the ReLU-masked gradient g and the pre-BN output z of the layer, and is
 // also written back over g so that the input-gradient convolution that follows reads dz directly.
 namespace wg {
+#ifndef F2F_WG_DZ_ROWS
+#define F2F_WG_DZ_ROWS 4
+#endif
 // Tile = TR output rows x 16 pixels.  The producers are latency-bound (one DRAM round trip per tile and warp:
 // ncu shows 47 % of the samples on the first use of the loaded registers), so the pipeline is made deep rather than
 // wide: small tiles, FOUR stages, and TWO producer groups that fill alternate tiles -- every group has two tiles of
@@ -900,7 +944,8 @@ constexpr int NGROUPS = 2;              // producer groups (tile it is staged by
 constexpr int OFF_BAR = STAGES * STAGE;
 constexpr int SMEM_BYTES = OFF_BAR + 128;
 constexpr int MMA_WARP = 8;
-constexpr int NTHREADS = (9 + 8 * (NGROUPS - 1)) * 32;   // group 0: warps 0-7, MMA: warp 8, group 1: warps 9-16
+constexpr int PF_WARP = 9 + 8 * (NGROUPS - 1);           // L2 prefetch warp
+constexpr int NTHREADS = (PF_WARP + 1) * 32;             // group 0: warps 0-7, MMA: warp 8, group 1: warps 9-16, prefetch: warp 17
 constexpr int TMEM_COLS = 512;
 constexpr int PARTIAL = 6 * 128 * 64;   // floats per CTA
 constexpr int HPIX = HR * 18, DPIX = TR * 16;
@@ -917,13 +962,21 @@ struct Args {
     int m64;               // taps ky = 2 as M = 64 instructions (F2F_WGRAD_M64)
     int rev;               // tile order: 1 = bottom-up (f2f_common.cuh, g_tile_rev)
     int pf;                // L2 prefetch distance, in tiles of a producer group (0: off; F2F_WGRAD_PF)
-    int dbg;               // -DF2F_WG_DEBUG builds only (tools/perf_wgrad.py): bit 0 no MMAs, 1 no activation loads,
-                           // 2 no g/z loads, 3 no dz write-back, 4 no shared-memory stores, 5 no transform arithmetic
+    unsigned long long *trace;   // -DF2F_WG_DEBUG builds only: role trace, see WG_T below
+    int dbg;               // -DF2F_WG_DEBUG builds only (tools/perf_wgrad.py): bit 0 = the MMA warp issues no MMAs
 };
 #ifdef F2F_WG_DEBUG
 #define WG_DBG(bit) ((a.dbg >> (bit)) & 1)
+// role trace of the debug build (f2f_dncnn_set_trace, tools/perf_wgrad.py): cycles summed over the CTAs, lane 0 of the first
+// activation / dz producer warp of group 0 and the MMA issuer.  [0..4] activation producer: issuing loads, waiting
+// for a free stage, loads landing (bit 6 set: all loaded registers are touched first), transform + stores, fence + arrive;
+// [5..9] the same for the dz producer; [10] MMA warp waiting for a full stage, [11] issuing; [12..14] tiles of the three roles
+#define WG_T(var) const long long var = clock64()
+#define WG_ACC(slot, val) do { if (tr_on) tr_acc[slot] += (val); } while (0)
 #else
 #define WG_DBG(bit) 0
+#define WG_T(var)
+#define WG_ACC(slot, val)
 #endif
 
 // The producers below are register-staged (load -> transform -> one shared-memory store) and were bound by the DRAM
@@ -941,10 +994,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a, const __grid_co
     const uint32_t bar0 = smem_u32(bars);
     auto BAR = [&](int i) { return bar0 + 8u * i; };   // full[STAGES] @0, empty[STAGES] @STAGES, done @2*STAGES; tmem ptr after
     uint32_t *tmem_ptr = reinterpret_cast<uint32_t *>(bars + 2 * STAGES + 2);
+    volatile int *progress = reinterpret_cast<volatile int *>(tmem_ptr + 2);   // [group]: the tile (of the CTA) the group is staging
 
     if (threadIdx.x == 0) {
+        // full: one arrival per producer thread (a per-warp arrival behind __syncwarp measured 20 % slower)
         for (int s = 0; s < STAGES; s++) { mbar_init(BAR(s), 256); mbar_init(BAR(STAGES + s), 1); }
         mbar_init(BAR(2 * STAGES), 1);
+        progress[0] = progress[1] = 0;
         mbar_fence_init();
     }
     if (warp == MMA_WARP) tmem_alloc(smem_u32(tmem_ptr), TMEM_COLS);
@@ -961,72 +1017,110 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a, const __grid_co
     pdl_wait();                  // set-up above overlapped the predecessor's tail (f2f_common.cuh)
     if (a.pdl_trigger) pdl_launch_dependents();
 
-    // role of this warp: producer warp index pw in 0..7 of group grp, or the MMA warp
-    const int grp = warp > MMA_WARP ? 1 : 0;
-    const int pw = warp > MMA_WARP ? warp - (MMA_WARP + 1) : warp;
+    // role of this warp: producer warp index pw in 0..7 of group grp, the MMA warp, or the prefetch warp
+    const int grp = (warp > MMA_WARP && warp != PF_WARP) ? 1 : 0;
+    const int pw = warp == PF_WARP ? 8 : warp > MMA_WARP ? warp - (MMA_WARP + 1) : warp;
 
     if (warp != MMA_WARP && pw < 4) {
         // ===== producer of the activation tile (HR x 18 halo) =====
-        const int ptid = pw * 32 + lane, chunk = ptid & 7;
-        float sc[8], sh[8];
+        // A thread owns one 8-channel chunk of one of the 16 regular columns and walks that column's HR halo rows: a
+        // row's address is the previous one plus an image row, the shared-memory destination a compile-time offset
+        // from a per-thread base; tiles that lie inside the image (all but the frame's border) take a path without
+        // any bounds predicate.  The 2 x HR x 8 elements of halo columns 16 and 17 are one item for every thread plus
+        // one more for the first 32.  (The first version spent 65 instructions per 16-byte element, 20 of them
+        // arithmetic on the data, and the role trace -- tools/perf_wgrad.py, -DF2F_WG_DEBUG -- showed the kernel bound
+        // by its producers' instruction stream: knocking the MMAs out did not change its time.)
+        const int ptid = pw * 32 + lane, chunk = ptid & 7, c = ptid >> 3;
+        float2 sc[4], sh[4];
 #pragma unroll
-        for (int j = 0; j < 8; j++) {
-            sc[j] = a.coef_in ? a.coef_in[C_SCALE + chunk * 8 + j] : 1.0f;
-            sh[j] = a.coef_in ? a.coef_in[C_SHIFT + chunk * 8 + j] : 0.0f;
+        for (int j = 0; j < 4; j++) {
+            sc[j] = a.coef_in ? make_float2(a.coef_in[C_SCALE + chunk * 8 + 2 * j], a.coef_in[C_SCALE + chunk * 8 + 2 * j + 1]) : make_float2(1.f, 1.f);
+            sh[j] = a.coef_in ? make_float2(a.coef_in[C_SHIFT + chunk * 8 + 2 * j], a.coef_in[C_SHIFT + chunk * 8 + 2 * j + 1]) : make_float2(0.f, 0.f);
         }
         const bool bn = a.coef_in != nullptr;
-        const bool pf_lane = a.pf > 0 && pw == 0 && lane == 0;
-        auto prefetch_act = [&](int tf) {
-            if (tf < ntiles) {
-                const int tp = a.rev ? ntiles - 1 - tf : tf;
-                tma_prefetch_l2_3d(&tm_act, 0, (tp % a.tiles_x) * 16 - 1, (tp / a.tiles_x) * TR - 1);
+        const ptrdiff_t rowpitch = (ptrdiff_t)a.W * 64;                 // elements between image rows
+        const int xrow = ptid >> 4, xcol = 16 + ((ptid >> 3) & 1);      // extra items: rows xrow and (ptid < 32) 8 + xrow
+        const bool x1 = ptid < (HR - 8) * 16;
+        const uint32_t soff = chunk * A_S + c * 16, xoff = xrow * A_R + chunk * A_S + xcol * 16;
+        // BatchNorm + ReLU of layer k-1 on the 8 channels of one element (two channels per packed FP32 FMA)
+        auto xf = [&](const uint4 &v) {
+            const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+            uint32_t o[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const float2 r = ffma2(unpack_h16(w[j]), sc[j], sh[j]);
+                o[j] = pack_h16_relu(r.x, r.y);
             }
+            return make_uint4(o[0], o[1], o[2], o[3]);
         };
-        if (pf_lane) {
-            tma_prefetch_desc(&tm_act);
-            for (int j = 0; j < a.pf; j++) prefetch_act(blockIdx.x + (grp + j * NGROUPS) * gridDim.x);
-        }
+#ifdef F2F_WG_DEBUG
+        const bool tr_on = a.trace && grp == 0 && pw == 0 && lane == 0;
+        long long tr_acc[5] = {0, 0, 0, 0, 0};
+        unsigned tr_tiles = 0;
+#endif
         int it = grp;
         for (int tile = blockIdx.x + grp * gridDim.x; tile < ntiles; tile += NGROUPS * gridDim.x, it += NGROUPS) {
             const int s = it % STAGES;
-            if (pf_lane) prefetch_act(tile + a.pf * NGROUPS * gridDim.x);
-            mbar_wait(BAR(STAGES + s), ((it / STAGES) & 1) ^ 1);
-            uint8_t *dstA = smem + s * STAGE;
+            WG_T(t_a);
             const int tpos = a.rev ? ntiles - 1 - tile : tile;
             const int ty0 = (tpos / a.tiles_x) * TR - 1, tx0 = (tpos % a.tiles_x) * 16 - 1;
-            constexpr int U = (HPIX + 15) / 16;   // the whole tile's loads in flight at once
-            uint4 v[U];
-            uint32_t inb = 0;
+            const h16 *base = a.act + ((ptrdiff_t)ty0 * a.W + tx0) * 64 + chunk * 8;
+            uint8_t *dstA = smem + s * STAGE;
+            uint4 v[HR + 2];
+            v[HR + 1] = make_uint4(0, 0, 0, 0);
+            if (ty0 >= 0 && tx0 >= 0 && ty0 + HR <= a.H && tx0 + 18 <= a.W) {      // warp-uniform: the tile and its halo lie inside
 #pragma unroll
-            for (int u = 0; u < U; u++) {
-                const int pix = (ptid >> 3) + 16 * u;
-                const int gy = ty0 + pix / 18, gx = tx0 + pix % 18;
-                v[u] = make_uint4(0, 0, 0, 0);
-                if (pix < HPIX && gy >= 0 && gy < a.H && gx >= 0 && gx < a.W && !WG_DBG(1)) {
-                    inb |= 1u << u;
-                    v[u] = __ldg(reinterpret_cast<const uint4 *>(a.act + ((size_t)gy * a.W + gx) * 64 + chunk * 8));
+                for (int u = 0; u < HR; u++) v[u] = __ldg(reinterpret_cast<const uint4 *>(base + u * rowpitch + c * 64));
+                v[HR] = __ldg(reinterpret_cast<const uint4 *>(base + xrow * rowpitch + xcol * 64));
+                if (x1) v[HR + 1] = __ldg(reinterpret_cast<const uint4 *>(base + (8 + xrow) * rowpitch + xcol * 64));
+                WG_T(t_b);
+                mbar_wait(BAR(STAGES + s), ((it / STAGES) & 1) ^ 1);      // the loads above are already in flight
+                WG_T(t_c);
+                if (bn) {
+#pragma unroll
+                    for (int u = 0; u < HR + 2; u++) v[u] = xf(v[u]);
+                }
+                WG_ACC(0, t_b - t_a); WG_ACC(1, t_c - t_b);
+            } else {
+                const bool colok = (unsigned)(tx0 + c) < (unsigned)a.W, xcolok = (unsigned)(tx0 + xcol) < (unsigned)a.W;
+                uint32_t inb = 0;
+#pragma unroll
+                for (int u = 0; u < HR; u++) {
+                    const bool ok = colok && (unsigned)(ty0 + u) < (unsigned)a.H;
+                    v[u] = make_uint4(0, 0, 0, 0);
+                    if (ok) v[u] = __ldg(reinterpret_cast<const uint4 *>(base + u * rowpitch + c * 64));
+                    inb |= (uint32_t)ok << u;
+                }
+                const bool ok0 = xcolok && (unsigned)(ty0 + xrow) < (unsigned)a.H;
+                const bool ok1 = x1 && xcolok && (unsigned)(ty0 + 8 + xrow) < (unsigned)a.H;
+                v[HR] = make_uint4(0, 0, 0, 0);
+                if (ok0) v[HR] = __ldg(reinterpret_cast<const uint4 *>(base + xrow * rowpitch + xcol * 64));
+                if (ok1) v[HR + 1] = __ldg(reinterpret_cast<const uint4 *>(base + (8 + xrow) * rowpitch + xcol * 64));
+                inb |= ((uint32_t)ok0 << HR) | ((uint32_t)ok1 << (HR + 1));
+                mbar_wait(BAR(STAGES + s), ((it / STAGES) & 1) ^ 1);
+                if (bn) {                                                  // positions outside the image stay zero
+#pragma unroll
+                    for (int u = 0; u < HR + 2; u++) v[u] = ((inb >> u) & 1u) ? xf(v[u]) : make_uint4(0, 0, 0, 0);
                 }
             }
+            WG_T(t_d);
 #pragma unroll
-            for (int u = 0; u < U; u++) {
-                const int pix = (ptid >> 3) + 16 * u;
-                if (pix < HPIX) {
-                    uint4 o = v[u];
-                    if (bn && ((inb >> u) & 1u) && !WG_DBG(5)) {
-                        uint32_t w[4] = {o.x, o.y, o.z, o.w};
-#pragma unroll
-                        for (int j = 0; j < 4; j++) {
-                            const float2 f = unpack_h16(w[j]);
-                            w[j] = pack_h16_relu(fmaf(f.x, sc[2 * j], sh[2 * j]), fmaf(f.y, sc[2 * j + 1], sh[2 * j + 1]));
-                        }
-                        o = make_uint4(w[0], w[1], w[2], w[3]);
-                    }
-                    if (!WG_DBG(4)) *reinterpret_cast<uint4 *>(dstA + (pix / 18) * A_R + chunk * A_S + (pix % 18) * 16) = o;
-                }
-            }
+            for (int u = 0; u < HR; u++) *reinterpret_cast<uint4 *>(dstA + soff + u * A_R) = v[u];
+            *reinterpret_cast<uint4 *>(dstA + xoff) = v[HR];
+            if (x1) *reinterpret_cast<uint4 *>(dstA + xoff + 8 * A_R) = v[HR + 1];
+            WG_T(t_e);
             fence_proxy_async();
             mbar_arrive(BAR(s));
+#ifdef F2F_WG_DEBUG
+            { WG_T(t_f); WG_ACC(3, t_e - t_d); WG_ACC(4, t_f - t_e); tr_tiles++; }
+#endif
         }
+#ifdef F2F_WG_DEBUG
+        if (tr_on) {
+            for (int q = 0; q < 5; q++) atomicAdd(a.trace + q, (unsigned long long)tr_acc[q]);
+            atomicAdd(a.trace + 12, (unsigned long long)tr_tiles);
+        }
+#endif
         if (grp == 0) {
             // ===== after the last tile: accumulators -> this CTA's partial (warps 0-3 = the four TMEM lane quadrants) =====
             mbar_wait(BAR(2 * STAGES), 0);
@@ -1053,78 +1147,130 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a, const __grid_co
                 }
             }
         }
-    } else if (warp != MMA_WARP) {
-        // ===== producer of the dz tile (TR x 16, no halo); writes dz back over g =====
-        const int ptid = (pw - 4) * 32 + lane, chunk = ptid & 7;
-        float cA[8], cB[8], cC[8];
-#pragma unroll
-        for (int j = 0; j < 8; j++) {
-            cA[j] = a.coef[C_A + chunk * 8 + j]; cB[j] = a.coef[C_B + chunk * 8 + j]; cC[j] = a.coef[C_C + chunk * 8 + j];
-        }
-        const bool pf_lane = a.pf > 0 && pw == 4 && lane == 0;
-        auto prefetch_dz = [&](int tf) {
-            if (tf < ntiles) {
+    } else if (warp == PF_WARP) {
+        // ===== L2 prefetch of the tiles ahead (one lane): the TMA unit pulls the activation halo box and the g / z boxes
+        // of CTA tile q into L2 once the producer group that will stage it has started the tile pf group-tiles earlier.
+        // A thread of its own, because a cp.async.bulk.prefetch.tensor can hold its issuing thread for ~1000 cycles
+        // (measured with the role trace while producer lanes issued them).
+        if (lane == 0 && a.pf > 0) {
+            tma_prefetch_desc(&tm_act);
+            tma_prefetch_desc(&tm_g);
+            tma_prefetch_desc(&tm_z);
+            for (int q = NGROUPS;; q++) {
+                const int tf = blockIdx.x + q * gridDim.x;
+                if (tf >= ntiles) break;
+                while (*(progress + (q % NGROUPS)) < q - NGROUPS * a.pf) __nanosleep(64);
                 const int tp = a.rev ? ntiles - 1 - tf : tf;
                 const int px = (tp % a.tiles_x) * 16, py = (tp / a.tiles_x) * TR;
                 tma_prefetch_l2_3d(&tm_g, 0, px, py);
                 tma_prefetch_l2_3d(&tm_z, 0, px, py);
+                tma_prefetch_l2_3d(&tm_act, 0, px - 1, py - 1);
             }
-        };
-        if (pf_lane) {
-            tma_prefetch_desc(&tm_g);
-            tma_prefetch_desc(&tm_z);
-            for (int j = 0; j < a.pf; j++) prefetch_dz(blockIdx.x + (grp + j * NGROUPS) * gridDim.x);
         }
+    } else if (warp != MMA_WARP) {
+        // ===== producer of the dz tile (TR x 16, no halo); writes dz back over g =====
+        // same thread -> (column, chunk) assignment as the activation producer; rows in passes of F2F_WG_DZ_ROWS
+        const int ptid = (pw - 4) * 32 + lane, chunk = ptid & 7, c = ptid >> 3;
+        float2 cA[4], cB[4], cC[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            cA[j] = make_float2(a.coef[C_A + chunk * 8 + 2 * j], a.coef[C_A + chunk * 8 + 2 * j + 1]);
+            cB[j] = make_float2(a.coef[C_B + chunk * 8 + 2 * j], a.coef[C_B + chunk * 8 + 2 * j + 1]);
+            cC[j] = make_float2(a.coef[C_C + chunk * 8 + 2 * j], a.coef[C_C + chunk * 8 + 2 * j + 1]);
+        }
+        // dz = A * g + (B * z + C) on the 8 channels of one element: the fmaf(A, g, fmaf(B, z, C)) of the first version,
+        // two channels per packed FP32 FMA (same roundings)
+        auto xf = [&](const uint4 &g, const uint4 &z) {
+            const uint32_t gw[4] = {g.x, g.y, g.z, g.w}, zw[4] = {z.x, z.y, z.z, z.w};
+            uint32_t o[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const float2 r = ffma2(cA[j], unpack_h16(gw[j]), ffma2(cB[j], unpack_h16(zw[j]), cC[j]));
+                o[j] = pack_h16(r.x, r.y);
+            }
+            return make_uint4(o[0], o[1], o[2], o[3]);
+        };
+        const ptrdiff_t rowpitch = (ptrdiff_t)a.W * 64;
+        const uint32_t soff = chunk * D_S + c * 16;
+#ifdef F2F_WG_DEBUG
+        const bool tr_on = a.trace && grp == 0 && pw == 4 && lane == 0;
+        long long tr_acc[5] = {0, 0, 0, 0, 0};
+        unsigned tr_tiles = 0;
+#endif
         int it = grp;
         for (int tile = blockIdx.x + grp * gridDim.x; tile < ntiles; tile += NGROUPS * gridDim.x, it += NGROUPS) {
             const int s = it % STAGES;
-            if (pf_lane) prefetch_dz(tile + a.pf * NGROUPS * gridDim.x);
-            mbar_wait(BAR(STAGES + s), ((it / STAGES) & 1) ^ 1);
-            uint8_t *dstD = smem + s * STAGE + A_BYTES;
+            WG_T(t_a);
+            if (pw == 4 && lane == 0) *(progress + grp) = it;         // paces the prefetch warp
             const int tpos = a.rev ? ntiles - 1 - tile : tile;
             const int ty0 = (tpos / a.tiles_x) * TR, tx0 = (tpos % a.tiles_x) * 16;
-            constexpr int U = DPIX / 32;          // two passes of 4 rounds x 16 pixels (register budget: 17 warps -> 96 registers)
-#pragma unroll 1
-            for (int r0 = 0; r0 < DPIX / 16; r0 += U) {
-            uint4 vg[U], vz[U];
-            uint32_t inb = 0;
+            const ptrdiff_t o0 = ((ptrdiff_t)ty0 * a.W + tx0 + c) * 64 + chunk * 8;
+            uint8_t *dstD = smem + s * STAGE + A_BYTES + soff;
+            constexpr int U = F2F_WG_DZ_ROWS;     // rows in flight per thread (register budget: 96 registers per thread)
+            if (ty0 + TR <= a.H && tx0 + 16 <= a.W) {      // warp-uniform: the tile lies inside the image
+                // rolling window: U rows of g and z in flight; as soon as a row has been transformed its registers take
+                // the loads of row + U, so one memory latency is exposed per tile instead of one per pass of U rows
+                uint4 vg[U], vz[U];
 #pragma unroll
-            for (int u = 0; u < U; u++) {
-                const int pix = (ptid >> 3) + 16 * (r0 + u);
-                const int gy = ty0 + (pix >> 4), gx = tx0 + (pix & 15);
-                vg[u] = vz[u] = make_uint4(0, 0, 0, 0);
-                if (gy < a.H && gx < a.W && !WG_DBG(2)) {
-                    inb |= 1u << u;
-                    const size_t o = ((size_t)gy * a.W + gx) * 64 + chunk * 8;
-                    vg[u] = *reinterpret_cast<const uint4 *>(a.g + o);
-                    vz[u] = __ldg(reinterpret_cast<const uint4 *>(a.z + o));
+                for (int u = 0; u < U; u++) {
+                    vg[u] = *reinterpret_cast<const uint4 *>(a.g + o0 + u * rowpitch);
+                    vz[u] = __ldg(reinterpret_cast<const uint4 *>(a.z + o0 + u * rowpitch));
                 }
-            }
+                WG_T(t_b);
+                mbar_wait(BAR(STAGES + s), ((it / STAGES) & 1) ^ 1);      // the loads above are already in flight
+                WG_T(t_c);
 #pragma unroll
-            for (int u = 0; u < U; u++) {
-                const int pix = (ptid >> 3) + 16 * (r0 + u);
-                uint4 o = make_uint4(0, 0, 0, 0);
-                if ((inb >> u) & 1u) {
-                    const uint32_t gw[4] = {vg[u].x, vg[u].y, vg[u].z, vg[u].w};
-                    const uint32_t zw[4] = {vz[u].x, vz[u].y, vz[u].z, vz[u].w};
-                    uint32_t w[4] = {gw[0], gw[1], gw[2], gw[3]};
-#pragma unroll
-                    for (int j = 0; j < 4; j++) {
-                        if (WG_DBG(5)) break;
-                        const float2 gg = unpack_h16(gw[j]), zz = unpack_h16(zw[j]);
-                        w[j] = pack_h16(fmaf(cA[2 * j], gg.x, fmaf(cB[2 * j], zz.x, cC[2 * j])),
-                                         fmaf(cA[2 * j + 1], gg.y, fmaf(cB[2 * j + 1], zz.y, cC[2 * j + 1])));
+                for (int u = 0; u < TR; u++) {
+                    const uint4 o = xf(vg[u % U], vz[u % U]);
+                    if (u + U < TR) {
+                        vg[u % U] = *reinterpret_cast<const uint4 *>(a.g + o0 + (u + U) * rowpitch);
+                        vz[u % U] = __ldg(reinterpret_cast<const uint4 *>(a.z + o0 + (u + U) * rowpitch));
                     }
-                    o = make_uint4(w[0], w[1], w[2], w[3]);
-                    const int gy = ty0 + (pix >> 4), gx = tx0 + (pix & 15);
-                    if (!WG_DBG(3)) *reinterpret_cast<uint4 *>(a.g + ((size_t)gy * a.W + gx) * 64 + chunk * 8) = o;
+                    *reinterpret_cast<uint4 *>(a.g + o0 + u * rowpitch) = o;
+                    *reinterpret_cast<uint4 *>(dstD + u * D_R) = o;
                 }
-                if (!WG_DBG(4)) *reinterpret_cast<uint4 *>(dstD + (pix >> 4) * D_R + chunk * D_S + (pix & 15) * 16) = o;
+#ifdef F2F_WG_DEBUG
+                { WG_T(t_e); WG_ACC(0, t_b - t_a); WG_ACC(1, t_c - t_b); WG_ACC(3, t_e - t_c); }
+#endif
+            } else {
+                const bool colok = tx0 + c < a.W;
+#pragma unroll 1
+                for (int r0 = 0; r0 < TR; r0 += U) {
+                    uint4 vg[U], vz[U];
+                    uint32_t inb = 0;
+#pragma unroll
+                    for (int u = 0; u < U; u++) {
+                        const bool ok = colok && ty0 + r0 + u < a.H;
+                        vg[u] = vz[u] = make_uint4(0, 0, 0, 0);
+                        if (ok) {
+                            vg[u] = *reinterpret_cast<const uint4 *>(a.g + o0 + (r0 + u) * rowpitch);
+                            vz[u] = __ldg(reinterpret_cast<const uint4 *>(a.z + o0 + (r0 + u) * rowpitch));
+                        }
+                        inb |= (uint32_t)ok << u;
+                    }
+                    if (r0 == 0) mbar_wait(BAR(STAGES + s), ((it / STAGES) & 1) ^ 1);
+#pragma unroll
+                    for (int u = 0; u < U; u++) {
+                        const bool ok = (inb >> u) & 1u;
+                        const uint4 o = ok ? xf(vg[u], vz[u]) : make_uint4(0, 0, 0, 0);
+                        if (ok) *reinterpret_cast<uint4 *>(a.g + o0 + (r0 + u) * rowpitch) = o;
+                        *reinterpret_cast<uint4 *>(dstD + (r0 + u) * D_R) = o;
+                    }
+                }
             }
-            }
+            WG_T(t_f);
             fence_proxy_async();
             mbar_arrive(BAR(s));
+#ifdef F2F_WG_DEBUG
+            { WG_T(t_g); WG_ACC(4, t_g - t_f); tr_tiles++; }
+#endif
         }
+#ifdef F2F_WG_DEBUG
+        if (tr_on) {
+            for (int q = 0; q < 5; q++) atomicAdd(a.trace + 5 + q, (unsigned long long)tr_acc[q]);
+            atomicAdd(a.trace + 13, (unsigned long long)tr_tiles);
+        }
+#endif
     } else {
         // ===== MMA issuer: converged warp, the elected lane issues (see dncnn.cu) =====
         const uint32_t el = elect_one();
@@ -1134,10 +1280,17 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a, const __grid_co
         // descriptors differ only in the start-address field (low word, 16-byte units)
         const uint64_t ad0 = smem_desc(0, 128, A_S), bd0 = smem_desc(0, 128, D_S);
         const uint32_t a_hi = (uint32_t)(ad0 >> 32), b_hi = (uint32_t)(bd0 >> 32);
+#ifdef F2F_WG_DEBUG
+        const bool tr_on = a.trace && el;
+        long long tr_acc[2] = {0, 0};
+        unsigned tr_tiles = 0;
+#endif
         int it = 0;
         for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it++) {
             const int s = it % STAGES;
+            WG_T(t_a);
             mbar_wait(BAR(s), (it / STAGES) & 1);
+            WG_T(t_b);
             fence_after_sync();
             const uint32_t a_base = smem_u32(smem + s * STAGE);
             const uint32_t a_lo = (uint32_t)ad0 | ((a_base & 0x3FFFFu) >> 4);
@@ -1155,7 +1308,17 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_wgrad64(Args a, const __grid_co
             }
             if (el) mma_commit(BAR(STAGES + s));
             __syncwarp();
+#ifdef F2F_WG_DEBUG
+            { WG_T(t_c); WG_ACC(0, t_b - t_a); WG_ACC(1, t_c - t_b); tr_tiles++; }
+#endif
         }
+#ifdef F2F_WG_DEBUG
+        if (tr_on) {
+            atomicAdd(a.trace + 10, (unsigned long long)tr_acc[0]);
+            atomicAdd(a.trace + 11, (unsigned long long)tr_acc[1]);
+            atomicAdd(a.trace + 14, (unsigned long long)tr_tiles);
+        }
+#endif
         if (el) mma_commit(BAR(2 * STAGES));
         __syncwarp();
     }
@@ -1247,9 +1410,10 @@ static int wgrad64_scaled(const void *d_act, const float *d_coef_in, void *d_g, 
     a.m64 = m64;
     a.rev = g_tile_rev;
     // L2 prefetch distance of the producers (tiles of a producer group); 0 turns the prefetches off (A/B)
-    static const int pf = getenv("F2F_WGRAD_PF") ? atoi(getenv("F2F_WGRAD_PF")) : 2;
+    static const int pf = getenv("F2F_WGRAD_PF") ? atoi(getenv("F2F_WGRAD_PF")) : 1;
     a.pf = pf < 0 ? 0 : pf > 8 ? 8 : pf;
     a.dbg = getenv("F2F_WGRAD_DBG") ? atoi(getenv("F2F_WGRAD_DBG")) : 0;
+    a.trace = dn::g_conv_trace;
     CUtensorMap tm_act, tm_g, tm_z;
     int rc = dnt::make_tensor_map(&tm_act, d_act, H, W, 18, wg::HR);
     if (!rc) rc = dnt::make_tensor_map(&tm_g, d_g, H, W, 16, wg::TR);

@@ -277,6 +277,27 @@ __device__ __forceinline__ bool elect_one()
     return pred != 0;
 }
 
+// 32-byte read-only global load (LDG.256, sm_100): `p` must be 32-byte aligned
+__device__ __forceinline__ void ldg256(const void *p, uint4 &lo, uint4 &hi)
+{
+    asm volatile("ld.global.nc.v8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(lo.x), "=r"(lo.y), "=r"(lo.z), "=r"(lo.w), "=r"(hi.x), "=r"(hi.y), "=r"(hi.z), "=r"(hi.w)
+                 : "l"(p));
+}
+
+// two FP32 fused multiply-adds in one instruction (fma.rn.f32x2, sm_100): d = a * b + c per component, IEEE rounding
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c)
+{
+    float2 d;
+    asm("{\n\t.reg .b64 ra, rb, rc, rd;\n\t"
+        "mov.b64 ra, {%2, %3};\n\tmov.b64 rb, {%4, %5};\n\tmov.b64 rc, {%6, %7};\n\t"
+        "fma.rn.f32x2 rd, ra, rb, rc;\n\t"
+        "mov.b64 {%0, %1}, rd;\n\t}"
+        : "=f"(d.x), "=f"(d.y)
+        : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y), "f"(c.x), "f"(c.y));
+    return d;
+}
+
 #ifndef F2F_STORE_BF16
 __device__ __forceinline__ uint32_t pack_h16(float lo, float hi)
 {

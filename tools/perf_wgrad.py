@@ -43,3 +43,18 @@ torch.cuda.synchronize()
 us = e0.elapsed_time(e1) / n * 1e3
 print("wgrad64 %dx%d: %.1f us per launch incl. the partial reduction (%d back to back), DBG=%s PF=%s"
       % (W, H, us, n, os.environ.get("F2F_WGRAD_DBG", "0"), os.environ.get("F2F_WGRAD_PF", "default")))
+
+if os.environ.get("F2F_WGRAD_TRACE"):
+    tr = torch.zeros(16, dtype=torch.int64, device=dev)
+    lib.f2f_dncnn_set_trace(tr.data_ptr())
+    launch(0)
+    torch.cuda.synchronize()
+    lib.f2f_dncnn_set_trace(None)
+    t = tr.cpu().tolist()
+    names = ["issue loads", "wait free stage", "loads landing", "transform+stores", "fence+arrive"]
+    for role, o, n in (("act producer", 0, t[12]), ("dz producer ", 5, t[13])):
+        n = max(n, 1)
+        print("  %s (group 0, per tile of the group): " % role + ", ".join("%s %d" % (names[i], t[o + i] / n) for i in range(5))
+              + "  = %d cycles, %d tiles" % (sum(t[o:o + 5]) / n, n))
+    n = max(t[14], 1)
+    print("  MMA warp (per tile): wait full stage %d, issue %d = %d cycles, %d tiles" % (t[10] / n, t[11] / n, (t[10] + t[11]) / n, n))
