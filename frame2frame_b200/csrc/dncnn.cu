@@ -358,6 +358,35 @@ k_conv64t(ConvArgs a, const __grid_constant__ CUtensorMap tm_in, const __grid_co
             uint8_t *st = smem + OFF_A + s * A_STAGE;
             mbar_wait(BAR(B_RAW_A + s), (it / NA) & 1);
             constexpr int ROUNDS = (HPIX + 15) / 16;                      // 16 pixels per round of 128 threads
+            if (ty0 >= 0 && tx0 >= 0 && ty0 + HH <= a.H && tx0 + HW <= a.W) {
+                // the haloed tile lies inside the image (all tiles but the frame's border; warp-uniform): no bounds
+                // arithmetic, and since 16 pixels further down the tile the swizzle phase (pix & 7) is the same, every
+                // element of the thread sits at a compile-time offset from one per-thread address
+                uint8_t *mine = st + (xt >> 3) * 128 + ((chunk ^ ((xt >> 3) & 7)) << 4);
+                constexpr int FULL = HPIX / 16;                           // rounds every thread takes part in
+#pragma unroll
+                for (int u = 0; u < ROUNDS; u++) {
+                    if (u < FULL || (xt >> 3) + 16 * u < HPIX) {
+                        const uint4 q = *reinterpret_cast<const uint4 *>(mine + u * 2048);
+                        const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+                        uint32_t o[4];
+#pragma unroll
+                        for (int j = 0; j < 4; j++) {
+                            const float2 r = ffma2(unpack_h16(w[j]), make_float2(sc[2 * j], sc[2 * j + 1]), make_float2(sh[2 * j], sh[2 * j + 1]));
+                            o[j] = pack_h16_relu(r.x, r.y);
+                        }
+                        *reinterpret_cast<uint4 *>(mine + u * 2048) = make_uint4(o[0], o[1], o[2], o[3]);
+                    }
+                }
+                fence_proxy_async();
+                if (PAIR) {
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive_cluster(mapa_u32(BAR(B_FULL_A + s), 0));
+                } else {
+                    mbar_arrive(BAR(B_FULL_A + s));
+                }
+                continue;
+            }
             uint4 v[ROUNDS];
             uint32_t ok = 0;
 #pragma unroll
