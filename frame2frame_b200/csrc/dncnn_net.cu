@@ -259,6 +259,11 @@ __global__ void __launch_bounds__(NT, 1) k_last_bwd(const float *__restrict__ dy
     float acc[22];   // [0,18): dW16[tap][j]; [18,20): sum g; [20,22): sum g*xhat
 #pragma unroll
     for (int i = 0; i < 22; i++) acc[i] = 0.0f;
+    float2 w2[9], acc2[9];                                   // both channels of the lane per register pair
+#pragma unroll
+    for (int t = 0; t < 9; t++) { w2[t] = make_float2(w[t][0], w[t][1]); acc2[t] = make_float2(0.0f, 0.0f); }
+    const float2 sc2 = make_float2(sc[0], sc[1]), sh2 = make_float2(sh[0], sh[1]);
+    const float2 is2 = make_float2(is[0], is[1]), ms2 = make_float2(ms[0], ms[1]);
     __syncthreads();
     if (threadIdx.x == 0 && blockIdx.x < ntiles)
         stage_tile(smem_u32(smem), bar0, z, (blockIdx.x / tiles_x) * TH, (blockIdx.x % tiles_x) * TW, H, W);
@@ -276,28 +281,46 @@ __global__ void __launch_bounds__(NT, 1) k_last_bwd(const float *__restrict__ dy
             const uint8_t *zrow = smem + s * ZSTAGE + r * ZROW + lane * 4;
             h16 *grow = g + ((size_t)y * W + tx0) * 64 + c0;
             const float *d2 = dnS + (r + 2) * XW + 2;       // dn[ky][kx] at d2[-ky * XW - kx + x]
-#pragma unroll 4
-            for (int x = xh; x < min(xh + 32, nx); x++) {
-                const float2 zz = unpack_h16(*reinterpret_cast<const uint32_t *>(zrow + x * 128));
-                const float y0 = fmaf(zz.x, sc[0], sh[0]), y1 = fmaf(zz.y, sc[1], sh[1]);
-                const float a0 = fmaxf(y0, 0.0f), a1 = fmaxf(y1, 0.0f);
-                float s0 = 0.0f, s1 = 0.0f;
+            // four pixels per step: their 3 x 6 window of dn is read once (4.5 instead of 9 shared-memory loads per
+            // pixel) and every multiply-add handles the lane's two channels at once (packed FP32 FMA; same
+            // per-component operations in the same order as the scalar version)
+            const int xend = min(xh + 32, nx);
+            for (int x = xh; x < xend; x += 4) {
+                float2 dv[3][6];                             // dv[ky][i] = dn at row -ky, column x - 2 + i (both halves)
 #pragma unroll
-                for (int t = 0; t < 9; t++) {
-                    const float dn = d2[x - (t / 3) * XW - (t % 3)];
-                    s0 = fmaf(dn, w[t][0], s0); s1 = fmaf(dn, w[t][1], s1);
-                    acc[2 * t] = fmaf(a0, dn, acc[2 * t]); acc[2 * t + 1] = fmaf(a1, dn, acc[2 * t + 1]);
+                for (int ky = 0; ky < 3; ky++)
+#pragma unroll
+                    for (int i = 0; i < 6; i++) {
+                        const float v = d2[x - 2 + i - ky * XW];
+                        dv[ky][i] = make_float2(v, v);
+                    }
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    if (x + i >= xend) break;
+                    const float2 zz = unpack_h16(*reinterpret_cast<const uint32_t *>(zrow + (x + i) * 128));
+                    const float2 yv = ffma2(zz, sc2, sh2);
+                    const float2 av = make_float2(fmaxf(yv.x, 0.0f), fmaxf(yv.y, 0.0f));
+                    float2 sv = make_float2(0.0f, 0.0f);
+#pragma unroll
+                    for (int t = 0; t < 9; t++) {
+                        const float2 dn = dv[t / 3][i + 2 - (t % 3)];
+                        sv = ffma2(dn, w2[t], sv);
+                        acc2[t] = ffma2(av, dn, acc2[t]);
+                    }
+                    const uint32_t o = pack_h16(yv.x > 0.0f ? sv.x : 0.0f, yv.y > 0.0f ? sv.y : 0.0f);
+                    *reinterpret_cast<uint32_t *>(grow + (size_t)(x + i) * 64) = o;
+                    const float2 gr = unpack_h16(o);             // sums of the ROUNDED gradient, like the tcgen05 epilogue
+                    acc[18] += gr.x; acc[19] += gr.y;
+                    const float2 xh2 = ffma2(zz, is2, ms2);
+                    acc[20] = fmaf(gr.x, xh2.x, acc[20]);
+                    acc[21] = fmaf(gr.y, xh2.y, acc[21]);
                 }
-                const uint32_t o = pack_h16(y0 > 0.0f ? s0 : 0.0f, y1 > 0.0f ? s1 : 0.0f);
-                *reinterpret_cast<uint32_t *>(grow + (size_t)x * 64) = o;
-                const float2 gr = unpack_h16(o);             // sums of the ROUNDED gradient, like the tcgen05 epilogue
-                acc[18] += gr.x; acc[19] += gr.y;
-                acc[20] = fmaf(gr.x, fmaf(zz.x, is[0], ms[0]), acc[20]);
-                acc[21] = fmaf(gr.y, fmaf(zz.y, is[1], ms[1]), acc[21]);
             }
         }
         __syncthreads();                                     // stage s and dnS are free again
     }
+#pragma unroll
+    for (int t = 0; t < 9; t++) { acc[2 * t] = acc2[t].x; acc[2 * t + 1] = acc2[t].y; }
     block_pair_reduce<22>(acc, reinterpret_cast<float *>(smem), [&](int l, int i) -> double * {
         if (i < 18) return dw16 + (2 * l + (i & 1)) * 9 + (i >> 1);
         if (i < 20) return stats + 2 * l + (i - 18);
@@ -315,8 +338,9 @@ __global__ void __launch_bounds__(NT, 1) k_first_wgrad(const h16 *__restrict__ g
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, r = warp >> 1, xh = (warp & 1) * 32;
     if (threadIdx.x == 0) { mbar_init(bar0, 1); mbar_init(bar0 + 8, 1); mbar_fence_init(); }
     float acc[18];
+    float2 acc2[9];
 #pragma unroll
-    for (int i = 0; i < 18; i++) acc[i] = 0.0f;
+    for (int t = 0; t < 9; t++) acc2[t] = make_float2(0.0f, 0.0f);
     __syncthreads();
     if (threadIdx.x == 0 && blockIdx.x < ntiles)
         stage_tile(smem_u32(smem), bar0, g0, (blockIdx.x / tiles_x) * TH, (blockIdx.x % tiles_x) * TW, H, W);
@@ -333,18 +357,29 @@ __global__ void __launch_bounds__(NT, 1) k_first_wgrad(const h16 *__restrict__ g
         if (y < H) {
             const uint8_t *grow = smem + s * ZSTAGE + r * ZROW + lane * 4;
             const float *x0 = xS + r * XW;                   // x[p + (ky-1, kx-1)] at x0[ky * XW + kx + x]
-#pragma unroll 4
-            for (int x_ = xh; x_ < min(xh + 32, nx); x_++) {
-                const float2 gg = unpack_h16(*reinterpret_cast<const uint32_t *>(grow + x_ * 128));
+            const int xend = min(xh + 32, nx);
+            for (int x_ = xh; x_ < xend; x_ += 4) {          // four pixels per step, as in k_last_bwd
+                float2 xv[3][6];
 #pragma unroll
-                for (int t = 0; t < 9; t++) {
-                    const float xv = x0[x_ + (t / 3) * XW + (t % 3)];
-                    acc[2 * t] = fmaf(gg.x, xv, acc[2 * t]); acc[2 * t + 1] = fmaf(gg.y, xv, acc[2 * t + 1]);
+                for (int ky = 0; ky < 3; ky++)
+#pragma unroll
+                    for (int i = 0; i < 6; i++) {
+                        const float v = x0[x_ + i + ky * XW];
+                        xv[ky][i] = make_float2(v, v);
+                    }
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    if (x_ + i >= xend) break;
+                    const float2 gg = unpack_h16(*reinterpret_cast<const uint32_t *>(grow + (x_ + i) * 128));
+#pragma unroll
+                    for (int t = 0; t < 9; t++) acc2[t] = ffma2(gg, xv[t / 3][i + t % 3], acc2[t]);
                 }
             }
         }
         __syncthreads();
     }
+#pragma unroll
+    for (int t = 0; t < 9; t++) { acc[2 * t] = acc2[t].x; acc[2 * t + 1] = acc2[t].y; }
     block_pair_reduce<18>(acc, reinterpret_cast<float *>(smem),
                           [&](int l, int i) -> double * { return dw0 + (2 * l + (i & 1)) * 9 + (i >> 1); });
 }
@@ -361,6 +396,9 @@ __global__ void __launch_bounds__(FT) k_first_fwd(const float *__restrict__ x, c
     for (int j = 0; j < 2; j++)
 #pragma unroll
         for (int t = 0; t < 9; t++) w[t][j] = w0[(c0 + j) * 9 + t];
+    float2 w2[9];
+#pragma unroll
+    for (int t = 0; t < 9; t++) w2[t] = make_float2(w[t][0], w[t][1]);
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         const int ty0 = (tile / tiles_x) * TH, tx0 = (tile % tiles_x) * TW;
         __syncthreads();
@@ -373,15 +411,23 @@ __global__ void __launch_bounds__(FT) k_first_fwd(const float *__restrict__ x, c
         if (y >= H) continue;
         const float *x0 = xS + r * XW;
         h16 *orow = a0 + ((size_t)y * W + tx0) * 64 + c0;
-#pragma unroll 4
-        for (int x_ = 0; x_ < nx; x_++) {
-            float s0 = 0.0f, s1 = 0.0f;
+        for (int x_ = 0; x_ < nx; x_ += 4) {                 // four pixels per step: 3 x 6 window, packed FP32 FMAs
+            float2 xv[3][6];
 #pragma unroll
-            for (int t = 0; t < 9; t++) {
-                const float xv = x0[x_ + (t / 3) * XW + (t % 3)];
-                s0 = fmaf(xv, w[t][0], s0); s1 = fmaf(xv, w[t][1], s1);
+            for (int ky = 0; ky < 3; ky++)
+#pragma unroll
+                for (int i = 0; i < 6; i++) {
+                    const float v = x0[x_ + i + ky * XW];
+                    xv[ky][i] = make_float2(v, v);
+                }
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                if (x_ + i >= nx) break;
+                float2 sv = make_float2(0.0f, 0.0f);
+#pragma unroll
+                for (int t = 0; t < 9; t++) sv = ffma2(xv[t / 3][i + t % 3], w2[t], sv);
+                *reinterpret_cast<uint32_t *>(orow + (size_t)(x_ + i) * 64) = pack_h16_relu(sv.x, sv.y);
             }
-            *reinterpret_cast<uint32_t *>(orow + (size_t)x_ * 64) = pack_h16_relu(s0, s1);
         }
     }
 }
