@@ -192,6 +192,9 @@ __global__ void k_adam(float *__restrict__ p, const float *__restrict__ g, float
 constexpr int LT = 16, LH = LT + 2, LHP = LH * LH;   // output tile / haloed tile of the 64->1 layer
 
 namespace rs {
+#ifndef F2F_LAST_SPLIT_A
+#define F2F_LAST_SPLIT_A 0   // 1: the last layer's activation operand as a 16-bit hi + lo pair as well (see k_last_fwd)
+#endif
 constexpr int TW = 64, TH = 8, NT = 512;            // tile, threads per block (16 warps: row = warp / 2, half = warp & 1)
 constexpr int ZROW = TW * 128, ZSTAGE = TH * ZROW;  // one staged row / tile of the NHWC BF16 image
 constexpr int XW = TW + 2, XH = TH + 2;             // haloed FP32 tile of the 1-channel image
@@ -455,12 +458,16 @@ struct LossFuse {
 // FP32 accumulate.  The layer is HBM-bound (128 bytes in, 4 out per pixel; N = 9 is far too narrow for tcgen05), the
 // point is to take the 640 FMAs and 150 warp-uniform shared-memory loads per pixel and lane off the CUDA cores, which
 // held the scalar version at 2.5x its HBM time.  A lane (g = lane / 4, t = lane % 4) loads channels [16t, 16t+16)
-// of pixels g and g+8 of a 16-pixel group (two 32-byte loads, every byte of the two 128-byte pixel rows used once), applies layer 15's BatchNorm+ReLU in FP32 and splits the result into a 16-bit value and the 16-bit
-// remainder, as the weights are split once per kernel: three products (hi*hi, lo*hi, hi*lo) keep the layer at FP32-class
-// precision like the CUDA-core version -- with single 16-bit operands the config0 trajectory of the online loop moved
-// by 0.06 dB on the second frame, past the 0.05 dB bar the default mode is held to there; the MMAs are nearly free in
-// this HBM-bound kernel.  The words feed the A fragment as they lie: the contraction does not care which channel sits
-// in which k slot as long as the B fragment uses the same assignment.
+// of pixels g and g+8 of a 16-pixel group (two 32-byte loads, every byte of the two 128-byte pixel rows used once),
+// applies layer 15's BatchNorm+ReLU in FP32 and rounds it to the 16-bit storage type -- the operand rounding every
+// 64->64 layer applies to its input -- while the WEIGHTS enter as a 16-bit value plus the 16-bit remainder (two
+// products per k-step): a rounded weight is the same error at every pixel, and with single 16-bit weights the config0
+// trajectory of the online loop moved by 0.06 dB on the second frame, past the 0.05 dB bar the default mode is held to
+// there.  -DF2F_LAST_SPLIT_A=1 splits the activation as well (three products, FP32-class like the CUDA-core version).
+// The words feed the A fragment as they lie: the contraction does not care which channel sits in which k slot as long
+// as the B fragment uses the same assignment.  The BatchNorm coefficients of the lane's 16 channels stay in registers:
+// read from shared memory (16 x 16 bytes per group) they made the L1/shared pipe the bound of the kernel (ncu: 83 %,
+// 26 M shared-memory wavefronts per launch; 143 -> 105 us with them in registers).
 __device__ __forceinline__ void mma16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1)
 {
 #ifndef F2F_STORE_BF16
@@ -486,18 +493,19 @@ __global__ void __launch_bounds__(256, MMA ? 2 : 1) k_last_fwd(const h16 *__rest
     __shared__ __align__(16) float cS[MMA ? 4 : 128];             // scale[64], shift[64]
     // MMA: this lane's 16 channels are c(h, j) = 16t + 8h + j; k-step (h, e) puts channels 4e + {0,1} in k slots
     // 2t + {0,1} and channels 4e + {2,3} in k slots 2t + 8 + {0,1}
-    __shared__ __align__(16) float cT[MMA ? 4 * 32 : 4];         // MMA: [t][scale of the lane's 16 channels | shift of them]
+    __shared__ __align__(16) float w8T[MMA ? 4 * 16 : 4];        // MMA: [t][tap-8 weight of the lane's 16 channels]
+    [[maybe_unused]] float sc[16], sh[16];                       // MMA: BatchNorm scale / shift of the lane's 16 channels
     // B fragments [k-step][register] of taps 0-7: w16 as a 16-bit hi part and the 16-bit remainder; tap 8 does not fit the
     // N = 8 tile and a second tile for one column doubles the mma.sync count, which bounds this kernel: it is an FP32
     // dot product over the lane's 16 channels and a 4-lane shuffle sum
     [[maybe_unused]] uint32_t bw[4][2], bl[4][2];
-    [[maybe_unused]] float w8[16];
     if constexpr (MMA) {
         const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
-        if (threadIdx.x < 128) {                         // coefficient table: the registers are needed for the fragments
-            const int tt = threadIdx.x >> 5, i = threadIdx.x & 31, cc = 16 * tt + (i & 15);
-            cT[threadIdx.x] = coef[(i < 16 ? C_SCALE : C_SHIFT) + cc];
-        }
+#pragma unroll
+        for (int i = 0; i < 16; i++) { sc[i] = coef[C_SCALE + 16 * t + i]; sh[i] = coef[C_SHIFT + 16 * t + i]; }
+        // tap 8's weights come from shared memory (4 x 16 bytes per group): the registers go to the coefficients, whose
+        // shared-memory reads (16 x 16 bytes per group when they lived there) had the kernel bound by the L1/shared pipe
+        if (threadIdx.x < 64) w8T[threadIdx.x] = w16[threadIdx.x * 9 + 8];
 #pragma unroll
         for (int ks = 0; ks < 4; ks++) {
             const int tap = g, c = 16 * t + 8 * (ks >> 1) + 4 * (ks & 1);
@@ -510,8 +518,7 @@ __global__ void __launch_bounds__(256, MMA ? 2 : 1) k_last_fwd(const h16 *__rest
                 bl[ks][i] = pack_h16(w0 - hf.x, w1 - hf.y);
             }
         }
-#pragma unroll
-        for (int i = 0; i < 16; i++) w8[i] = w16[(16 * t + i) * 9 + 8];
+
     } else {
         for (int e = threadIdx.x; e < 8 * 72; e += 256) {
             const int c = e / 72, t = (e % 72) >> 3, j = e & 7;
@@ -560,8 +567,15 @@ __global__ void __launch_bounds__(256, MMA ? 2 : 1) k_last_fwd(const h16 *__rest
 #pragma unroll
             for (int q = 0; q < 3; q++) {
                 if (warp + 8 * q >= NG) break;           // warp-uniform (warps 5-7 have no third group)
-                uint32_t aw[2][2][4], al[2][2][4];       // [pixel][half][word]: BatchNorm + ReLU in FP32 as 16-bit hi + remainder
+                uint32_t aw[2][2][4];                    // [pixel][half][word]: BatchNorm + ReLU in FP32, rounded to 16 bits
+                [[maybe_unused]] uint32_t al[2][2][4];   // F2F_LAST_SPLIT_A: the 16-bit remainder
                 float p8[2] = {0.0f, 0.0f};              // tap 8 of the two pixels, this lane's 16 channels (CUDA cores)
+                float w8v[16];
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    const float4 w = reinterpret_cast<const float4 *>(w8T + 16 * t)[i];
+                    w8v[4 * i] = w.x; w8v[4 * i + 1] = w.y; w8v[4 * i + 2] = w.z; w8v[4 * i + 3] = w.w;
+                }
 #pragma unroll
                 for (int r = 0; r < 2; r++) {
                     const int pix = (warp + 8 * q) * 16 + g + 8 * r;
@@ -570,20 +584,20 @@ __global__ void __launch_bounds__(256, MMA ? 2 : 1) k_last_fwd(const h16 *__rest
 #pragma unroll
                     for (int h = 0; h < 2; h++) {
                         const uint32_t w4[4] = {v[q & 1][r][h].x, v[q & 1][r][h].y, v[q & 1][r][h].z, v[q & 1][r][h].w};
-                        const float4 *ct = reinterpret_cast<const float4 *>(cT + t * 32 + h * 8);
-                        const float4 s0 = ct[0], s1 = ct[1], h0 = ct[4], h1 = ct[5];
-                        const float scv[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
-                        const float shv[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+                        const float *scv = sc + h * 8, *shv = sh + h * 8;
+                        const float *w8 = w8v + h * 8;
 #pragma unroll
                         for (int j = 0; j < 4; j++) {
                             const float2 f = unpack_h16(w4[j]);
                             const float a0 = fmaxf(fmaf(f.x, scv[2 * j], shv[2 * j]), 0.0f);
                             const float a1 = fmaxf(fmaf(f.y, scv[2 * j + 1], shv[2 * j + 1]), 0.0f);
                             const uint32_t pk = pack_h16(a0, a1);
-                            const float2 hf = unpack_h16(pk);
                             aw[r][h][j] = in ? pk : 0u;
+#if F2F_LAST_SPLIT_A
+                            const float2 hf = unpack_h16(pk);
                             al[r][h][j] = in ? pack_h16(a0 - hf.x, a1 - hf.y) : 0u;
-                            if (in) p8[r] = fmaf(a0, w8[h * 8 + 2 * j], fmaf(a1, w8[h * 8 + 2 * j + 1], p8[r]));
+#endif
+                            if (in) p8[r] = fmaf(a0, w8[2 * j], fmaf(a1, w8[2 * j + 1], p8[r]));
                         }
                     }
                 }
@@ -592,8 +606,10 @@ __global__ void __launch_bounds__(256, MMA ? 2 : 1) k_last_fwd(const h16 *__rest
 #pragma unroll
                 for (int ks = 0; ks < 4; ks++) {
                     const int h = ks >> 1, e = ks & 1;
-                    // a * w = (ah + al) * (wh + wl) without the al * wl term (2^-22 relative): the small products first
+                    // a * (wh + wl), the small product first (F2F_LAST_SPLIT_A: (ah + al) * (wh + wl) without al * wl)
+#if F2F_LAST_SPLIT_A
                     mma16816(d0, al[0][h][2 * e], al[1][h][2 * e], al[0][h][2 * e + 1], al[1][h][2 * e + 1], bw[ks][0], bw[ks][1]);
+#endif
                     mma16816(d0, aw[0][h][2 * e], aw[1][h][2 * e], aw[0][h][2 * e + 1], aw[1][h][2 * e + 1], bl[ks][0], bl[ks][1]);
                     mma16816(d0, aw[0][h][2 * e], aw[1][h][2 * e], aw[0][h][2 * e + 1], aw[1][h][2 * e + 1], bw[ks][0], bw[ks][1]);
                 }
