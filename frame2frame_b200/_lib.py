@@ -40,6 +40,7 @@ def _declare(lib):
     lib.f2f_tvl1_centered_gradient.argtypes = [fp, fp, fp, C.c_int, C.c_int, vp]
     lib.f2f_tvl1_normalize.argtypes = [fp, fp, fp, fp, C.c_int, C.c_int, vp, vp]
     lib.f2f_selftest_division.argtypes = [C.c_ulonglong, C.POINTER(C.c_ulonglong)]
+    lib.f2f_selftest_hypot.argtypes = [C.c_ulonglong, C.POINTER(C.c_ulonglong)]
     lib.f2f_warp_mask.argtypes = [fp, fp, fp, fp, fp, fp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp]
     lib.f2f_occlusion_mask.argtypes = [fp, fp, fp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp]
     lib.f2f_masked_loss.argtypes = [fp, fp, fp, fp, vp, sz, C.c_int, vp]

@@ -340,6 +340,10 @@ void f2f_profile_dncnn_read(double out[4]);
  * division on n pseudo-random operand pairs in the ranges the solver produces;
  * *h_mismatches receives the number of differing results (expected 0). */
 int f2f_selftest_division(unsigned long long n, unsigned long long *h_mismatches);
+/* The same for the dual update's (float)hypot(a, b) (tvl1flow_lib.c:247-248): the in-line correctly rounded double
+ * square root (no slow-path call) against the library sqrt(), float and double results, n pseudo-random gradient
+ * pairs incl. zeros; *h_mismatches receives the number of differing results (expected 0). */
+int f2f_selftest_hypot(unsigned long long n, unsigned long long *h_mismatches);
 
 
 /* Release every cached device allocation of the calling process. */

@@ -175,6 +175,15 @@ def test_inline_division_is_ieee(cuda):
     assert bad.value == 0
 
 
+def test_inline_hypot_is_the_library_square_root(cuda):
+    # the dual update's (float)hypot runs an in-line correctly rounded double square root (no slow-path call);
+    # float and double results must agree bit-for-bit with sqrt() on gradient pairs of every magnitude, incl. zeros
+    import ctypes as C
+    bad = C.c_ulonglong(123)
+    _lib.check(_lib.lib().f2f_selftest_hypot(1 << 30, C.byref(bad)), "selftest")
+    assert bad.value == 0
+
+
 def test_tvl1flow_command_lines(cuda, tmp_path):
     """The reference's command lines (main.c:86-99 positionals, tvl1flow.sh:9-19 sequence script) through
     frame2frame_b200.tvl1flow_cli: .flo files byte-compatible with readFlowFile.py, flows equal to the oracle's."""
