@@ -192,6 +192,32 @@ int main()
 // Issue-rate variants (timing only): how cheaply can 72 M128 N64 K16 MMAs with different operand
 // views be issued?  VAR 0: one thread (threadIdx.x == 0).  VAR 1: converged warp, predicated on
 // elect.  VAR 2: one elected thread of warp 0 (if (elect_one())).
+// weight-stationary form: tcgen05.mma.ws keeps the B operand in one of four collector buffers (fill / use / lastuse), so
+// consecutive MMAs with the SAME B and different A tiles (the convolution's case when several pixel tiles are in flight:
+// one tap's weights against each of them) read B from shared memory once.  USE: 0 fill, 1 use, 2 lastuse, 3 discard
+template <int USE>
+__device__ __forceinline__ void mma_ws(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate)
+{
+    if (USE == 0)
+        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                     "tcgen05.mma.ws.cta_group::1.kind::f16.collector::b0::fill [%0], %1, %2, %3, p;\n\t}"
+                     ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+    else if (USE == 1)
+        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                     "tcgen05.mma.ws.cta_group::1.kind::f16.collector::b0::use [%0], %1, %2, %3, p;\n\t}"
+                     ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+    else if (USE == 2)
+        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                     "tcgen05.mma.ws.cta_group::1.kind::f16.collector::b0::lastuse [%0], %1, %2, %3, p;\n\t}"
+                     ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+    else
+        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                     "tcgen05.mma.ws.cta_group::1.kind::f16.collector::b0::discard [%0], %1, %2, %3, p;\n\t}"
+                     ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+
+// VAR 3: .ws, every MMA discards its B (no reuse); VAR 4: .ws, B filled by the first and reused by the second MMA of a
+// pair; VAR 5: .ws, four A tiles per B (fill, use, use, lastuse; TMEM columns 0..255)
 template <int VAR>
 __global__ void __launch_bounds__(128, 1) k_issue(int reps, long long *cycles)
 {
@@ -201,7 +227,7 @@ __global__ void __launch_bounds__(128, 1) k_issue(int reps, long long *cycles)
     uint32_t *tmem_ptr = (uint32_t *)(bar + 2);
     for (int i = threadIdx.x; i < (A_BYTES + 9 * B_TAP) / 16; i += blockDim.x) ((uint4 *)smem)[i] = make_uint4(0, 0, 0, 0);
     if (threadIdx.x == 0) { mbar_init(smem_u32(bar), 1); mbar_fence_init(); }
-    if (threadIdx.x < 32) tmem_alloc(smem_u32(tmem_ptr), 128);
+    if (threadIdx.x < 32) tmem_alloc(smem_u32(tmem_ptr), VAR == 5 ? 256 : 128);
     fence_proxy_async();
     fence_before_sync();
     __syncthreads();
@@ -225,6 +251,13 @@ __global__ void __launch_bounds__(128, 1) k_issue(int reps, long long *cycles)
                     for (int h = 0; h < 2; h++) {
                         const uint64_t ad = ((uint64_t)a_hi << 32) | (a_lo + ((tap / 3) * HWD + tap % 3) * 8 + h * 64 + j * 2);
                         if (VAR == 1) mma_ss_el(tmem + h * 64, ad, bd, IDESC, (rep | tap | j) != 0, el);
+                        else if (VAR == 3) mma_ws<3>(tmem + h * 64, ad, bd, IDESC, (rep | tap | j) != 0);
+                        else if (VAR == 4) { if (h == 0) mma_ws<0>(tmem, ad, bd, IDESC, (rep | tap | j) != 0); else mma_ws<2>(tmem + 64, ad, bd, IDESC, (rep | tap | j) != 0); }
+                        else if (VAR == 5) {
+                            // two more A views of the same staged tile stand in for tiles 3 and 4
+                            if (h == 0) { mma_ws<0>(tmem, ad, bd, IDESC, (rep | tap | j) != 0); mma_ws<1>(tmem + 128, ad + 8, bd, IDESC, (rep | tap | j) != 0); }
+                            else { mma_ws<1>(tmem + 64, ad, bd, IDESC, (rep | tap | j) != 0); mma_ws<2>(tmem + 192, ad + 8, bd, IDESC, (rep | tap | j) != 0); }
+                        }
                         else mma_ss(tmem + h * 64, ad, bd, IDESC, (rep | tap | j) != 0);
                     }
                 }
@@ -240,7 +273,7 @@ __global__ void __launch_bounds__(128, 1) k_issue(int reps, long long *cycles)
     }
     fence_before_sync();
     __syncthreads();
-    if (threadIdx.x < 32) tmem_dealloc(tmem, 128);
+    if (threadIdx.x < 32) tmem_dealloc(tmem, VAR == 5 ? 256 : 128);
 }
 
 template <int VAR>
@@ -253,13 +286,18 @@ static void run_issue(long long *d_cyc)
     cudaMemcpy(cyc.data(), d_cyc, 148 * 8, cudaMemcpyDeviceToHost);
     double avg = 0;
     for (int i = 0; i < 148; i++) avg += cyc[i];
-    printf("issue variant %d: %.1f cycles per MMA (%s)\n", VAR, avg / 148 / (reps * 72), cudaGetErrorString(cudaGetLastError()));
+    printf("issue variant %d: %.1f cycles per MMA (%s)\n", VAR, avg / 148 / (reps * (VAR == 5 ? 144 : 72)), cudaGetErrorString(cudaGetLastError()));
 }
 
 void issue_variants(long long *d_cyc)
 {
     run_issue<0>(d_cyc);
     run_issue<1>(d_cyc);
+    if (getenv("UBENCH_WS")) {     // weight-stationary forms (timing only)
+        run_issue<3>(d_cyc);
+        run_issue<4>(d_cyc);
+        run_issue<5>(d_cyc);
+    }
 }
 
 // ---------------------------------------------------------------------------------------------
